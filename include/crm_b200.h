@@ -1,0 +1,189 @@
+/*
+ * crm_b200.h — C ABI of the B200-native colony-mechanics path.
+ *
+ * This is the drop-in boundary beneath the Python surface of cr_mech_coli
+ * (crm.Configuration / crm.AgentSettings / crm.generate_agents /
+ * crm.run_simulation_with_agents -> CellContainer).  The reference has no
+ * C-ABI of its own: its boundary is the PyO3 module `cr_mech_coli.cr_mech_coli`
+ * (reference src/lib.rs:46-116).  Every entry point below names the reference
+ * interface it replaces (file:line relative to the reference tree).
+ *
+ * Conventions: plain pointers and sizes only; the caller owns host buffers,
+ * the library owns device buffers; every function returns 0 on success or a
+ * negative crm_status; crm_last_error() returns the message of the last
+ * failure on the calling thread.  No exceptions cross the ABI.
+ *
+ * Array layouts at the boundary are those of the Python API: a rod's
+ * position is an (n_vertices, 3) row-major f32 matrix (numpy layout of
+ * RodAgent.pos, reference src/agent.rs:520-525); N rods are N such matrices
+ * back to back.
+ */
+#ifndef CRM_B200_H
+#define CRM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRM_ABI_VERSION 1
+
+typedef enum crm_status {
+    CRM_OK = 0,
+    CRM_ERR_INVALID = -1,   /* bad argument / configuration                    */
+    CRM_ERR_CUDA = -2,      /* CUDA runtime failure                            */
+    CRM_ERR_BOUNDARY = -3,  /* "Particle is out of domain" (BoundaryError)     */
+    CRM_ERR_NUMERIC = -4,   /* NaN/Inf in the state (CalcError)                */
+    CRM_ERR_DIVISION = -5,  /* division failed (DivisionError)                 */
+    CRM_ERR_TIME = -6,      /* invalid time configuration (TimeError)          */
+    CRM_ERR_NOMEM = -7
+} crm_status;
+
+/* Interaction potential variants: reference src/agent.rs:272-277 (enum PhysInt). */
+enum { CRM_POT_MORSE = 0, CRM_POT_MIE = 1 };
+/* Setter variants: reference src/agent.rs:11-35 / :104-112
+ * (GrowthRateSetter / SpringLengthThresholdSetter: NormalDistr{mean,std} | Explicit{a,b}). */
+enum { CRM_SETTER_NORMAL = 0, CRM_SETTER_EXPLICIT = 1 };
+/* CellIdentifier variants (cellular_raza CellIdentifier; reference
+ * cr_mech_coli/cr_mech_coli.pyi:81-95, src/crm_fit/predict.rs:267,
+ * src/crm_divide.rs:219).  The numeric order is the sort order. */
+enum { CRM_ID_DIVISION = 0, CRM_ID_INITIAL = 1, CRM_ID_INSERTED = 2 };
+
+/* Replaces `Configuration` (reference src/config.rs:395-465). */
+typedef struct crm_config {
+    float t0;
+    float dt;
+    float t_max;
+    uint32_t n_saves;
+    float domain_size[2];
+    float domain_height;
+    uint32_t n_voxels[2];
+    uint64_t rng_seed;
+    float gel_pressure;
+    float surface_friction;
+    float surface_friction_distance;
+    uint32_t n_threads; /* accepted, ignored: the device replaces the rayon pool */
+} crm_config;
+
+/* Per-rod scalar state: the non-matrix fields of `RodAgent`
+ * (reference src/agent.rs:212-239; RodMechanics fields src/config.rs:63-84;
+ * potentials src/agent.rs:323-339). */
+typedef struct crm_rod_params {
+    float diffusion_constant;
+    float spring_tension;
+    float rigidity;
+    float spring_length;
+    float damping;
+    int32_t potential;          /* CRM_POT_* */
+    float radius;
+    float strength;
+    float cutoff;
+    float potential_stiffness;  /* Morse only */
+    float bound;                /* Mie only   */
+    float en;                   /* Mie only   */
+    float em;                   /* Mie only   */
+    uint32_t n_neighbors;       /* PhysicalInteraction.1 */
+    float growth_rate;
+    int32_t growth_setter_kind; /* CRM_SETTER_* */
+    float growth_setter_a;      /* mean | g1 */
+    float growth_setter_b;      /* std  | g2 */
+    float spring_length_threshold;
+    int32_t threshold_setter_kind;
+    float threshold_setter_a;   /* mean | l1 */
+    float threshold_setter_b;   /* std  | l2 */
+    int32_t has_neighbor_reduction;
+    uint32_t neighbor_reduction_max;
+    float neighbor_reduction_exp;
+} crm_rod_params;
+
+/* CellIdentifier: Initial(n) -> {CRM_ID_INITIAL, 0, n};
+ * Division(voxel, counter) -> {CRM_ID_DIVISION, voxel, counter}.
+ * kind < 0 encodes `None` (no parent). */
+typedef struct crm_ident {
+    int64_t kind;
+    uint64_t voxel;
+    uint64_t counter;
+} crm_ident;
+
+typedef struct crm_sim crm_sim;
+
+/* ---- library ---------------------------------------------------------- */
+int crm_abi_version(void);
+const char* crm_last_error(void);
+/* Number of visible CUDA devices (<0: CUDA unavailable). */
+int crm_device_count(void);
+
+/* ---- host helpers on the boundary ------------------------------------ */
+/* Replaces `counter_to_color` / `color_to_counter` (reference src/imaging.rs:28-66). */
+void crm_counter_to_color(uint32_t counter, uint8_t rgb[3]);
+uint32_t crm_color_to_counter(const uint8_t rgb[3]);
+
+/* Replaces `_generate_positions` (reference src/simulation.rs:107-166):
+ * ChaCha8 + rand-0.9 stream-exact placement.  out_pos: [n_agents][n_vertices][3]. */
+int crm_generate_positions(uint32_t n_agents, float spring_length, const crm_config* config,
+                           uint64_t rng_seed, const float dx[2], float randomize_positions,
+                           uint32_t n_vertices, float* out_pos);
+
+/* Save schedule of `run_simulation_with_agents` (reference src/simulation.rs:239-249;
+ * cellular_raza FixedStepsize::from_partial_save_points).  Writes at most `cap`
+ * iteration indices, returns the number of distinct save iterations (or <0);
+ * *n_iterations receives the index of the last iteration. */
+int crm_save_schedule(const crm_config* config, uint64_t* out_iterations, uint32_t cap,
+                      uint64_t* n_iterations);
+
+/* ---- simulation object ------------------------------------------------ */
+/* Replaces the setup half of `run_simulation_with_agents`
+ * (reference src/simulation.rs:234-292): domain, stepper, storage. */
+int crm_sim_create(const crm_config* config, int device, crm_sim** out);
+void crm_sim_destroy(crm_sim* sim);
+
+/* Agents are copied in (reference moves `Vec<RodAgent>` by value,
+ * src/simulation.rs:234-237).  pos/vel: [n_rods][n_vertices][3] host f32. */
+int crm_sim_set_agents(crm_sim* sim, const float* pos, const float* vel,
+                       const crm_rod_params* params, uint32_t n_rods, uint32_t n_vertices);
+
+/* The whole of `run_main!` (reference src/simulation.rs:283-292): steps to
+ * t_max, snapshots at the save iterations into host memory owned by `sim`. */
+int crm_sim_run(crm_sim* sim);
+
+/* Advance `n_steps` mechanics steps without taking snapshots (bench / tests). */
+int crm_sim_step(crm_sim* sim, uint32_t n_steps);
+
+/* Force accumulators the next step would use, i.e. the reference's
+ * interaction + domain force for the current state (cellular_raza
+ * update_mechanics_interaction_step_1..3 + calculate_custom_domain_force).
+ * out_force: [n_rods][n_vertices][3]; out_n_neighbors: [n_rods] (either may be NULL). */
+int crm_sim_compute_forces(crm_sim* sim, float* out_force, uint32_t* out_n_neighbors);
+
+uint32_t crm_sim_n_rods(const crm_sim* sim);
+uint32_t crm_sim_n_vertices(const crm_sim* sim);
+uint64_t crm_sim_iteration(const crm_sim* sim);
+
+/* Current state in slot order (any pointer may be NULL). */
+int crm_sim_get_state(crm_sim* sim, float* pos, float* vel, crm_rod_params* params,
+                      crm_ident* ids, crm_ident* parents);
+
+/* Snapshots taken by crm_sim_run: what `storage.cells.load_all_elements()`
+ * yields in the reference (src/simulation.rs:293-306). */
+uint32_t crm_sim_n_snapshots(const crm_sim* sim);
+int crm_sim_snapshot_info(const crm_sim* sim, uint32_t k, uint64_t* iteration, uint32_t* n_rods);
+int crm_sim_snapshot_copy(const crm_sim* sim, uint32_t k, float* pos, float* vel,
+                          crm_rod_params* params, crm_ident* ids, crm_ident* parents);
+
+/* Counters for the bench harness: kernels launched by this sim so far and
+ * the rod-steps it has advanced. */
+uint64_t crm_sim_launch_count(const crm_sim* sim);
+uint64_t crm_sim_rod_steps(const crm_sim* sim);
+/* Device time (ms, CUDA events on the sim's stream) spent in the force kernel
+ * and in all kernels since the last call to crm_sim_reset_timers; the number of
+ * interacting ordered rod pairs of the last force launch (for the roofline). */
+int crm_sim_enable_timers(crm_sim* sim, int enable);
+int crm_sim_read_timers(crm_sim* sim, double* force_ms, uint64_t* force_launches,
+                        uint64_t* last_pairs_in_cutoff, uint64_t* last_pairs_tested);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CRM_B200_H */
