@@ -1,0 +1,733 @@
+// crm_kernels.cu — hand-written sm_100a kernels of the colony-mechanics step.
+//
+//   k_bin_count / k_bin_scan / k_bin_scatter   centroid cell list (counting sort)
+//   k_force<NV>         gather-style rod-rod interaction + neighbour sensing + domain force
+//   k_integrate<NV>     springs + bending + damping, Adams-Bashforth, growth, boundary
+//   k_divide<NV>        division geometry for the (host-ordered) list of dividing rods
+//   k_pack / k_unpack   boundary layout <-> device layout
+//
+// Thread mapping everywhere: LP lanes per rod (lane = vertex), 32/LP rods per warp.
+#include "crm_device.cuh"
+
+namespace crm {
+
+#define FULL 0xffffffffu
+
+// ------------------------------------------------------------------------------------
+// layout conversion: boundary [n][nv][3]  <->  device [n][3][LP]
+template <int NV>
+__global__ void k_unpack(const float* __restrict__ src, float* __restrict__ dst, uint32_t n) {
+    constexpr int LP = Lay<NV>::LP;
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t rod = tid / (3 * LP);
+    uint32_t rem = tid % (3 * LP);
+    if (rod >= n) return;
+    uint32_t c = rem / LP, i = rem % LP;
+    dst[(size_t)rod * 3 * LP + rem] = (i < NV) ? src[((size_t)rod * NV + i) * 3 + c] : 0.0f;
+}
+
+template <int NV>
+__global__ void k_pack(const float* __restrict__ src, float* __restrict__ dst, uint32_t n) {
+    constexpr int LP = Lay<NV>::LP;
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t rod = tid / (3 * NV);
+    uint32_t rem = tid % (3 * NV);
+    if (rod >= n) return;
+    uint32_t i = rem / 3, c = rem % 3;
+    dst[(size_t)rod * 3 * NV + rem] = src[(size_t)rod * 3 * LP + c * LP + i];
+}
+
+// ------------------------------------------------------------------------------------
+// group helpers
+template <int LP>
+__device__ __forceinline__ unsigned group_mask() {
+    if (LP == 32) return FULL;
+    unsigned lane = threadIdx.x & 31;
+    return ((1u << LP) - 1u) << (lane / LP * LP);
+}
+template <int LP>
+__device__ __forceinline__ float group_sum(float v, unsigned m) {
+#pragma unroll
+    for (int o = LP / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o, LP);
+    return v;
+}
+template <int LP>
+__device__ __forceinline__ float group_max(float v, unsigned m) {
+#pragma unroll
+    for (int o = LP / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(m, v, o, LP));
+    return v;
+}
+
+// centroid + extent of a rod held one vertex per lane
+template <int NV>
+__device__ __forceinline__ float4 bounding_sphere(float x, float y, float z, int l, unsigned m) {
+    constexpr int LP = Lay<NV>::LP;
+    bool v = l < NV;
+    float cx = group_sum<LP>(v ? x : 0.0f, m) * (1.0f / NV);
+    float cy = group_sum<LP>(v ? y : 0.0f, m) * (1.0f / NV);
+    float cz = group_sum<LP>(v ? z : 0.0f, m) * (1.0f / NV);
+    float dx = x - cx, dy = y - cy, dz = z - cz;
+    float e2 = v ? dx * dx + dy * dy + dz * dz : 0.0f;
+    float e = sqrtf(group_max<LP>(e2, m));
+    return make_float4(cx, cy, cz, e * 1.000001f + 1e-6f);
+}
+
+// ------------------------------------------------------------------------------------
+// bounding spheres of the current state + max extent (used after set_agents)
+template <int NV>
+__global__ void k_bounds(Dev d) {
+    constexpr int LP = Lay<NV>::LP;
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t a = tid / LP;
+    int l = threadIdx.x % LP;
+    unsigned m = group_mask<LP>();
+    if (a >= d.n) return;  // whole groups exit together
+    const float* p = d.pos + (size_t)a * 3 * LP;
+    float x = p[l], y = p[LP + l], z = p[2 * LP + l];
+    float4 bs = bounding_sphere<NV>(x, y, z, l, m);
+    if (l == 0) {
+        d.bsphere[a] = bs;
+        atomicMax(&d.status->emax_bits, __float_as_uint(bs.w));
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// cell list over rod centroids
+__device__ __forceinline__ int cell_index(const Dev& d, float cx, float cy) {
+    int ix = (int)floorf(cx * d.inv_wx), iy = (int)floorf(cy * d.inv_wy);
+    ix = min(max(ix, 0), d.ncx - 1);
+    iy = min(max(iy, 0), d.ncy - 1);
+    return iy * d.ncx + ix;
+}
+
+__global__ void k_bin_count(Dev d) {
+    uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= d.n) return;
+    float4 bs = d.bsphere[a];
+    int c = cell_index(d, bs.x, bs.y);
+    d.cell_of[a] = (uint32_t)c;
+    d.cell_rank[a] = atomicAdd(&d.cell_count[c], 1u);
+}
+
+// single-block exclusive scan of cell_count -> cell_start (ncells + 1 entries)
+__global__ void k_bin_scan(Dev d, uint32_t ncells) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry_s;
+    const uint32_t T = blockDim.x;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < ncells; base += T) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = (i < ncells) ? d.cell_count[i] : 0u;
+        uint32_t s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(FULL, s, o);
+            if ((threadIdx.x & 31) >= (unsigned)o) s += t;
+        }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = s;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = (threadIdx.x < (T >> 5)) ? warp_tot[threadIdx.x] : 0u;
+            uint32_t ws = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t t = __shfl_up_sync(FULL, ws, o);
+                if (threadIdx.x >= (unsigned)o) ws += t;
+            }
+            warp_tot[threadIdx.x] = ws - w;  // exclusive
+        }
+        __syncthreads();
+        uint32_t carry = carry_s;
+        uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + s - v;
+        if (i < ncells) d.cell_start[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == T - 1) carry_s = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) d.cell_start[ncells] = carry_s;
+}
+
+__global__ void k_bin_scatter(Dev d) {
+    uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= d.n) return;
+    d.sorted[d.cell_start[d.cell_of[a]] + d.cell_rank[a]] = a;
+}
+
+// The atomic ranks are arrival-ordered; sorting each cell's entries by slot makes
+// the candidate order (and with it the f32 summation order) reproducible.
+__global__ void k_bin_sort(Dev d, uint32_t ncells) {
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    uint32_t s = d.cell_start[c], e = d.cell_start[c + 1];
+    for (uint32_t i = s + 1; i < e; ++i) {
+        uint32_t v = d.sorted[i];
+        uint32_t j = i;
+        while (j > s && d.sorted[j - 1] > v) {
+            d.sorted[j] = d.sorted[j - 1];
+            --j;
+        }
+        d.sorted[j] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// force kernel.  Rod A = sorted[group]; lane l owns vertex l and segment (l, l+1).
+// For every candidate rod B of the 3x3 cell stencil that passes the bounding-sphere
+// test, the group evaluates
+//   own part: vertex a_l against every segment of B with A's potential  -> F_A[l]
+//   ext part: every vertex of B against segment (a_l, a_l+1) with B's potential;
+//             the reaction is split (1-q, q) onto a_l / a_l+1
+// and sums 1/2 (own + ext): exactly the two half-weighted calculate_force_between
+// calls of the reference backend, gathered per rod so that no atomics are needed.
+template <int NV, bool FAST, bool COUNT>
+__global__ void __launch_bounds__(128) k_force(Dev d) {
+    constexpr int LP = Lay<NV>::LP;
+    constexpr int STRIDE = Lay<NV>::STRIDE;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t g = tid / LP;
+    const int l = threadIdx.x % LP;
+    const unsigned gm = group_mask<LP>();
+    if (g >= d.n) return;
+    const uint32_t a = d.sorted[g];
+
+    const float* pa = d.pos + (size_t)a * STRIDE;
+    const float ax = pa[l], ay = pa[LP + l], az = pa[2 * LP + l];
+    // own segment (a_l, a_l+1)
+    const float qx = __shfl_down_sync(gm, ax, 1, LP), qy = __shfl_down_sync(gm, ay, 1, LP),
+                qz = __shfl_down_sync(gm, az, 1, LP);
+    const float sx = qx - ax, sy = qy - ay, sz = qz - az;
+    const float slen2 = sx * sx + sy * sy + sz * sz;
+    const float sinv = fast_rcp(slen2);
+    const bool has_vertex = l < NV;
+    const bool has_segment = l < NV - 1;
+
+    const PotParams potA = d.pot[a];
+    const float4 bsA = d.bsphere[a];
+    const float sense_r = potA.radius;
+
+    float fx = 0.f, fy = 0.f, fz = 0.f;     // own share on vertex l
+    float lx = 0.f, ly = 0.f, lz = 0.f;     // ext share landing on vertex l   (weight 1-q)
+    float hx = 0.f, hy = 0.f, hz = 0.f;     // ext share landing on vertex l+1 (weight q)
+    uint32_t count = 0;
+    unsigned long long n_tested = 0, n_cut = 0;
+
+    const int cxa = min(max((int)floorf(bsA.x * d.inv_wx), 0), d.ncx - 1);
+    const int cya = min(max((int)floorf(bsA.y * d.inv_wy), 0), d.ncy - 1);
+
+    for (int cy = max(cya - 1, 0); cy <= min(cya + 1, d.ncy - 1); ++cy) {
+        // the three x-neighbour cells of one row are contiguous in the cell list
+        const int c0 = cy * d.ncx + max(cxa - 1, 0);
+        const int c1 = cy * d.ncx + min(cxa + 1, d.ncx - 1);
+        const uint32_t s = d.cell_start[c0], e = d.cell_start[c1 + 1];
+        for (uint32_t base = s; base < e; base += LP) {
+            const uint32_t idx = base + l;
+            uint32_t b = 0xffffffffu;
+            bool ok = false;
+            if (idx < e) {
+                b = d.sorted[idx];
+                if (b != a) {
+                    const float4 bs = d.bsphere[b];
+                    const float ddx = bs.x - bsA.x, ddy = bs.y - bsA.y, ddz = bs.z - bsA.z;
+                    const float lim = bsA.w + bs.w + d.rsearch;
+                    ok = ddx * ddx + ddy * ddy + ddz * ddz <= lim * lim;
+                }
+            }
+            unsigned hits = __ballot_sync(gm, ok);
+            hits = (LP == 32) ? hits : ((hits >> ((threadIdx.x & 31) / LP * LP)) & ((1u << LP) - 1u));
+            while (hits) {
+                const int k = __ffs(hits) - 1;
+                hits &= hits - 1;
+                const uint32_t bb = __shfl_sync(gm, b, k, LP);
+                const float* pb = d.pos + (size_t)bb * STRIDE;
+                const PotParams potB = d.pot[bb];
+                float bx[NV], by[NV], bz[NV];
+                if (LP % 4 == 0 && NV == LP) {
+                    const float4* p4 = reinterpret_cast<const float4*>(pb);
+#pragma unroll
+                    for (int q = 0; q < LP / 4; ++q) {
+                        float4 vx = __ldg(p4 + q), vy = __ldg(p4 + LP / 4 + q), vz = __ldg(p4 + 2 * (LP / 4) + q);
+                        bx[4 * q] = vx.x; bx[4 * q + 1] = vx.y; bx[4 * q + 2] = vx.z; bx[4 * q + 3] = vx.w;
+                        by[4 * q] = vy.x; by[4 * q + 1] = vy.y; by[4 * q + 2] = vy.z; by[4 * q + 3] = vy.w;
+                        bz[4 * q] = vz.x; bz[4 * q + 1] = vz.y; bz[4 * q + 2] = vz.z; bz[4 * q + 3] = vz.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < NV; ++q) {
+                        bx[q] = __ldg(pb + q);
+                        by[q] = __ldg(pb + LP + q);
+                        bz[q] = __ldg(pb + 2 * LP + q);
+                    }
+                }
+                const float R_own = potA.radius + potB.radius;
+                bool any_cut = false;
+                // ---- own part: a_l vs segments of B, potential of A
+                if (has_vertex) {
+#pragma unroll
+                    for (int j = 0; j < NV - 1; ++j) {
+                        const float ex = bx[j + 1] - bx[j], ey = by[j + 1] - by[j], ez = bz[j + 1] - bz[j];
+                        const float px = ax - bx[j], py = ay - by[j], pz = az - bz[j];
+                        const float dot = ex * px + ey * py + ez * pz;
+                        const float len2 = ex * ex + ey * ey + ez * ez;
+                        float t = FAST ? dot * fast_rcp(len2) : dot / len2;
+                        t = fminf(fmaxf(t, 0.0f), 1.0f);
+                        const float nx = bx[j] * (1.0f - t) + bx[j + 1] * t;
+                        const float ny = by[j] * (1.0f - t) + by[j + 1] * t;
+                        const float nz = bz[j] * (1.0f - t) + bz[j + 1] * t;
+                        const float zx = ax - nx, zy = ay - ny, zz = az - nz;
+                        const float r2 = zx * zx + zy * zy + zz * zz;
+                        const float sc = force_scale<FAST>(potA, R_own, r2);
+                        fx += zx * sc; fy += zy * sc; fz += zz * sc;
+                        if (COUNT) any_cut |= (r2 <= potA.cutoff * potA.cutoff);
+                    }
+                }
+                // ---- ext part: b_k vs segment (a_l, a_l+1), potential of B; reaction on A
+                if (has_segment) {
+#pragma unroll
+                    for (int q = 0; q < NV; ++q) {
+                        const float px = bx[q] - ax, py = by[q] - ay, pz = bz[q] - az;
+                        const float dot = sx * px + sy * py + sz * pz;
+                        float t = FAST ? dot * sinv : dot / slen2;
+                        t = fminf(fmaxf(t, 0.0f), 1.0f);
+                        const float nx = ax * (1.0f - t) + qx * t;
+                        const float ny = ay * (1.0f - t) + qy * t;
+                        const float nz = az * (1.0f - t) + qz * t;
+                        const float zx = bx[q] - nx, zy = by[q] - ny, zz = bz[q] - nz;
+                        const float r2 = zx * zx + zy * zy + zz * zz;
+                        const float sc = -force_scale<FAST>(potB, R_own, r2);  // reaction on A
+                        const float wl = sc * (1.0f - t), wh = sc * t;
+                        lx += zx * wl; ly += zy * wl; lz += zz * wl;
+                        hx += zx * wh; hy += zy * wh; hz += zz * wh;
+                    }
+                }
+                // ---- neighbour sensing (reference src/agent.rs:407-424)
+                bool near = false;
+                if (has_vertex) {
+                    const float thr = (sense_r + potB.radius) * 0.70710678118654752440f;
+                    const float thr2 = thr * thr;
+#pragma unroll
+                    for (int q = 0; q < NV; ++q) {
+                        const float ux = ax - bx[q], uy = ay - by[q], uz = az - bz[q];
+                        near |= (ux * ux + uy * uy + uz * uz) < thr2;
+                    }
+                }
+                count += (__ballot_sync(gm, near) & gm) ? 1u : 0u;
+                if (COUNT) {
+                    n_tested += 1;
+                    n_cut += (__ballot_sync(gm, any_cut) & gm) ? 1u : 0u;
+                }
+            }
+        }
+    }
+    // vertex l receives the q-share of segment l-1 from the lane below
+    float ux = __shfl_up_sync(gm, hx, 1, LP), uy = __shfl_up_sync(gm, hy, 1, LP), uz = __shfl_up_sync(gm, hz, 1, LP);
+    if (l == 0) { ux = 0.f; uy = 0.f; uz = 0.f; }
+    float Fx = 0.5f * (fx + lx + ux), Fy = 0.5f * (fy + ly + uy), Fz = 0.5f * (fz + lz + uz);
+    // domain force (CartesianSubDomainRods::calculate_custom_force)
+    Fz -= d.gel_pressure;
+    if (d.surface_friction != 0.0f && az <= d.surface_friction_distance) {
+        const float* va = d.vel + (size_t)a * STRIDE;
+        Fx -= d.surface_friction * va[l];
+        Fy -= d.surface_friction * va[LP + l];
+        Fz -= d.surface_friction * va[2 * LP + l];
+    }
+    if (has_vertex) {
+        float* f = d.force + (size_t)a * STRIDE;
+        f[l] = Fx; f[LP + l] = Fy; f[2 * LP + l] = Fz;
+    }
+    if (l == 0) {
+        d.nn[a] = count;
+        if (COUNT) {
+            atomicAdd(&d.status->pairs_tested, n_tested);
+            atomicAdd(&d.status->pairs_in_cutoff, n_cut);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// boundary reflection (CartesianSubDomainRods::apply_boundary)
+__device__ __forceinline__ bool reflect(float& p, float& v, float hi) {
+    if (p < 0.0f) { p = -p; v = fabsf(v); }
+    if (p > hi) { p = 2.0f * hi - p; v = -fabsf(v); }
+    return p >= 0.0f && p <= hi;
+}
+
+// fused mechanics: RodMechanics::calculate_increment + Adams-Bashforth(3) + Cycle::update_cycle
+// + boundary + bounding sphere of the new state.
+template <int NV>
+__global__ void __launch_bounds__(128) k_integrate(Dev d) {
+    constexpr int LP = Lay<NV>::LP;
+    constexpr int STRIDE = Lay<NV>::STRIDE;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t a = tid / LP;
+    const int l = threadIdx.x % LP;
+    const unsigned gm = group_mask<LP>();
+    if (a >= d.n) return;
+    const size_t o = (size_t)a * STRIDE;
+    const bool hv = l < NV;
+    const int li = hv ? l : 0;
+
+    float P[3], V[3], F[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        P[c] = d.pos[o + c * LP + li];
+        V[c] = d.vel[o + c * LP + li];
+        F[c] = d.force[o + c * LP + li];
+    }
+    const MechParams mp = d.mech[a];
+    GrowState gs = d.grow[a];
+    const float tension = mp.x, rigidity = mp.y, damping = mp.z, diffusion = mp.w;
+    const float L = gs.z;
+
+    // neighbours
+    float Pn[3], Pp[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        Pn[c] = __shfl_down_sync(gm, P[c], 1, LP);
+        Pp[c] = __shfl_up_sync(gm, P[c], 1, LP);
+    }
+    // spring of segment l (between l and l+1): force on vertex l
+    float fs[3] = {0.f, 0.f, 0.f};
+    float c2[3] = {P[0] - Pn[0], P[1] - Pn[1], P[2] - Pn[2]};  // conn_l = v_l - v_{l+1}
+    float n2 = sqrtf(c2[0] * c2[0] + c2[1] * c2[1] + c2[2] * c2[2]);
+    if (l < NV - 1 && n2 != 0.0f) {
+        float k = tension * (n2 - L);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) fs[c] = -(c2[c] / n2) * k;
+    }
+    // bending at interior vertex l
+    float fb[3] = {0.f, 0.f, 0.f};
+    {
+        float c1[3] = {Pp[0] - P[0], Pp[1] - P[1], Pp[2] - P[2]};  // conn_{l-1}
+        float n1 = sqrtf(c1[0] * c1[0] + c1[1] * c1[1] + c1[2] * c1[2]);
+        if (l >= 1 && l < NV - 1) {
+            float angle;
+            if (n1 == 0.0f || n2 == 0.0f) {
+                angle = 0.0f;
+            } else {
+                float cs = -(c1[0] * c2[0] + c1[1] * c2[1] + c1[2] * c2[2]) / (n1 * n2);
+                cs = fminf(fmaxf(cs, -1.0f), 1.0f);
+                angle = acosf(cs);
+            }
+            float fd[3] = {c1[0] / n1 - c2[0] / n2, c1[1] / n1 - c2[1] / n2, c1[2] / n1 - c2[2] / n2};
+            float nfd = sqrtf(fd[0] * fd[0] + fd[1] * fd[1] + fd[2] * fd[2]);
+            float scale = rigidity * (3.14159265358979323846f - angle);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) fb[c] = ((nfd == 0.0f) ? fd[c] : fd[c] / nfd) * scale;
+        }
+    }
+    float dv[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float fs_prev = __shfl_up_sync(gm, fs[c], 1, LP);
+        float fb_prev = __shfl_up_sync(gm, fb[c], 1, LP);
+        float fb_next = __shfl_down_sync(gm, fb[c], 1, LP);
+        if (l == 0) { fs_prev = 0.f; fb_prev = 0.f; }
+        if (l >= NV - 1) fb_next = 0.f;
+        float t = F[c];
+        t -= fs_prev;  // reaction of segment l-1
+        t += fs[c];
+        t -= 0.5f * fb_prev;
+        t += fb[c];
+        t -= 0.5f * fb_next;
+        t -= damping * V[c];
+        dv[c] = t;
+    }
+    // Adams-Bashforth over the stored increments
+    const int nh = d.nhist[a];
+    const float dt = d.dt;
+    const float c23 = 23.0f / 12.0f, c16 = 16.0f / 12.0f, c5 = 5.0f / 12.0f;
+    const float amp = (diffusion > 0.0f) ? sqrtf(2.0f * diffusion * dt) : 0.0f;
+    float Pnew[3], Vnew[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const size_t i = o + c * LP + li;
+        float x1 = d.dx1[i], v1 = d.dv1[i], x2 = d.dx2[i], v2 = d.dv2[i];
+        float ip, iv;
+        if (nh >= 2) {
+            ip = (c23 * V[c] - c16 * x1 + c5 * x2) * dt;
+            iv = (c23 * dv[c] - c16 * v1 + c5 * v2) * dt;
+        } else if (nh == 1) {
+            ip = (1.5f * V[c] - 0.5f * x1) * dt;
+            iv = (1.5f * dv[c] - 0.5f * v1) * dt;
+        } else {
+            ip = V[c] * dt;
+            iv = dv[c] * dt;
+        }
+        if (amp != 0.0f) {
+            float n0, n1;
+            normal_pair(d.seed, d.iteration, a, (uint64_t)(l * 3 + c), n0, n1);
+            ip += amp * n0;
+        }
+        if (hv) {
+            d.dx2[i] = x1; d.dv2[i] = v1;
+            d.dx1[i] = V[c]; d.dv1[i] = dv[c];
+        }
+        Pnew[c] = P[c] + ip;
+        Vnew[c] = V[c] + iv;
+    }
+    // Cycle::update_cycle (bit-exact ops: no FMA contraction, same order as the reference)
+    float rate = gs.x;
+    if (d.cyc[a].has_nr) {
+        const CycleParams cp = d.cyc[a];
+        float mx = (float)cp.nr_max, nnb = (float)d.nn[a];
+        rate = __fmul_rn(gs.x, powf(fmaxf(__fdiv_rn(__fsub_rn(mx, nnb), mx), 0.0f), cp.nr_exp));
+    }
+    const float newL = __fadd_rn(L, __fmul_rn(__fmul_rn(rate, dt), L));
+    const bool dividing = newL > gs.y;
+
+    bool inside = true;
+    if (!dividing) {  // dividing rods are reflected after the division (k_divide)
+        inside &= reflect(Pnew[0], Vnew[0], d.lx);
+        inside &= reflect(Pnew[1], Vnew[1], d.ly);
+        inside &= reflect(Pnew[2], Vnew[2], d.lz);
+    }
+    const bool finite = isfinite(Pnew[0]) && isfinite(Pnew[1]) && isfinite(Pnew[2]);
+    if (hv) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            d.pos[o + c * LP + l] = Pnew[c];
+            d.vel[o + c * LP + l] = Vnew[c];
+        }
+        if (!finite || !inside) {
+            if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
+                d.status->err_slot = a;
+        }
+    }
+    float4 bs = bounding_sphere<NV>(Pnew[0], Pnew[1], Pnew[2], l, gm);
+    if (dividing) {
+        // user voxel of the mother = voxel of the mean vertex at the start of the step,
+        // summed sequentially like the reference (nalgebra row_mean)
+        float mx = 0.f, my = 0.f;
+#pragma unroll
+        for (int q = 0; q < NV; ++q) {
+            mx = __fadd_rn(mx, __shfl_sync(gm, P[0], q, LP));
+            my = __fadd_rn(my, __shfl_sync(gm, P[1], q, LP));
+        }
+        if (l == 0) {
+            mx = __fdiv_rn(mx, (float)NV);
+            my = __fdiv_rn(my, (float)NV);
+            int ix = (int)floorf(__fdiv_rn(mx, d.uvx_w)), iy = (int)floorf(__fdiv_rn(my, d.uvy_w));
+            ix = min(max(ix, 0), d.unx - 1);
+            iy = min(max(iy, 0), d.uny - 1);
+            unsigned k = atomicAdd(&d.status->n_div, 1u);
+            if (k < d.divcap) {
+                d.divlist[k].slot = a;
+                d.divlist[k].uvox = (uint32_t)(ix * d.uny + iy);
+            } else {
+                d.status->overflow = 1;
+            }
+        }
+    }
+    if (l == 0) {
+        gs.z = newL;
+        d.grow[a] = gs;
+        if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
+        d.bsphere[a] = bs;
+        atomicMax(&d.status->emax_bits, __float_as_uint(bs.w));
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// division: RodMechanics::divide + Cycle::divide for the slot-ordered list of mothers.
+// Group r handles mother divlist[r]; daughter 1 stays in the mother's slot, daughter 2
+// goes to slot n0 + r.
+__device__ __forceinline__ float setter_sample(int kind, float a, float b, int which, uint64_t seed,
+                                               uint64_t it, uint64_t slot, uint64_t stream) {
+    if (kind == CRM_SETTER_EXPLICIT) return which == 0 ? a : b;
+    if (b == 0.0f) return a;
+    float n0, n1;
+    normal_pair(seed ^ 0xD1B54A32D192ED03ULL, it, slot, stream, n0, n1);
+    return a + b * (which == 0 ? n0 : n1);
+}
+
+template <int NV>
+__global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t n0) {
+    constexpr int LP = Lay<NV>::LP;
+    constexpr int STRIDE = Lay<NV>::STRIDE;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t r = tid / LP;
+    const int l = threadIdx.x % LP;
+    const unsigned gm = group_mask<LP>();
+    if (r >= n_div) return;
+    const uint32_t a = d.divlist[r].slot;
+    const uint32_t b = n0 + r;
+    const size_t oa = (size_t)a * STRIDE, ob = (size_t)b * STRIDE;
+    const bool hv = l < NV;
+    const int li = hv ? l : 0;
+    float P[3] = {d.pos[oa + li], d.pos[oa + LP + li], d.pos[oa + 2 * LP + li]};
+    float V[3] = {d.vel[oa + li], d.vel[oa + LP + li], d.vel[oa + 2 * LP + li]};
+    const PotParams pot = d.pot[a];
+    GrowState gs = d.grow[a];
+    const CycleParams cp = d.cyc[a];
+    // all vertices and segment lengths, replicated in every lane
+    float X[NV], Y[NV], Z[NV], seg[NV], cum[NV + 1];
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+        X[q] = __shfl_sync(gm, P[0], q, LP);
+        Y[q] = __shfl_sync(gm, P[1], q, LP);
+        Z[q] = __shfl_sync(gm, P[2], q, LP);
+    }
+    float total = 0.0f;
+    cum[0] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < NV - 1; ++q) {
+        float dx = X[q] - X[q + 1], dy = Y[q] - Y[q + 1], dz = Z[q] - Z[q + 1];
+        seg[q] = sqrtf(dx * dx + dy * dy + dz * dz);
+        total += seg[q];
+        cum[q + 1] = total;
+    }
+    const float seg_len = (total - 2.0f * pot.radius) / (float)(NV - 1) / 2.0f;
+    float D1[3] = {0.f, 0.f, 0.f}, D2[3] = {0.f, 0.f, 0.f};
+    {
+        // lane l computes vertex l of daughter 1 and vertex NV-1-n (n = NV-1-l) of daughter 2
+        const float s1 = (float)li * seg_len;
+        int k = 0;
+#pragma unroll
+        for (int j = 0; j < NV - 1; ++j)
+            if (cum[j] <= s1) k = j;
+        float ck = 0.f, sk = 1.f, x0 = 0.f, y0 = 0.f, z0 = 0.f, x1 = 0.f, y1 = 0.f, z1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV - 1; ++j)
+            if (j == k) { ck = cum[j]; sk = seg[j]; x0 = X[j]; y0 = Y[j]; z0 = Z[j]; x1 = X[j + 1]; y1 = Y[j + 1]; z1 = Z[j + 1]; }
+        float q = (s1 - ck) / sk;
+        D1[0] = x0 * (1.0f - q) + x1 * q;
+        D1[1] = y0 * (1.0f - q) + y1 * q;
+        D1[2] = z0 * (1.0f - q) + z1 * q;
+        // daughter 2: vertex index l corresponds to n = NV-1-l steps from the end
+        const float s2 = (float)(NV - 1 - li) * seg_len;
+        float cr = 0.0f, cm = 0.0f;
+        int m = 0;
+#pragma unroll
+        for (int j = 0; j < NV - 1; ++j) {
+            if (cr <= s2) { m = j; cm = cr; }
+            cr += seg[NV - 2 - j];
+        }
+        float sm = 1.f;
+#pragma unroll
+        for (int j = 0; j < NV - 1; ++j)
+            if (j == m) { sm = seg[NV - 2 - j]; x0 = X[NV - 1 - j]; y0 = Y[NV - 1 - j]; z0 = Z[NV - 1 - j]; x1 = X[NV - 2 - j]; y1 = Y[NV - 2 - j]; z1 = Z[NV - 2 - j]; }
+        float p = (s2 - cm) / sm;
+        D2[0] = x0 * (1.0f - p) + x1 * p;
+        D2[1] = y0 * (1.0f - p) + y1 * p;
+        D2[2] = z0 * (1.0f - p) + z1 * p;
+    }
+    float V1[3] = {V[0], V[1], V[2]}, V2[3] = {V[0], V[1], V[2]};
+    bool inside = true;
+    inside &= reflect(D1[0], V1[0], d.lx); inside &= reflect(D1[1], V1[1], d.ly); inside &= reflect(D1[2], V1[2], d.lz);
+    inside &= reflect(D2[0], V2[0], d.lx); inside &= reflect(D2[1], V2[1], d.ly); inside &= reflect(D2[2], V2[2], d.lz);
+    const bool finite = isfinite(D1[0]) && isfinite(D1[1]) && isfinite(D1[2]) && isfinite(D2[0]) && isfinite(D2[1]) && isfinite(D2[2]);
+    if (hv) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            d.pos[oa + c * LP + l] = D1[c];
+            d.vel[oa + c * LP + l] = V1[c];
+            d.pos[ob + c * LP + l] = D2[c];
+            d.vel[ob + c * LP + l] = V2[c];
+        }
+        if (!finite || !inside) {
+            if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
+                d.status->err_slot = a;
+        }
+    }
+    // the new cell starts with an empty increment history
+    {
+        const int lz = threadIdx.x % LP;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            d.dx1[ob + c * LP + lz] = 0.f; d.dv1[ob + c * LP + lz] = 0.f;
+            d.dx2[ob + c * LP + lz] = 0.f; d.dv2[ob + c * LP + lz] = 0.f;
+            d.force[ob + c * LP + lz] = 0.f;
+        }
+    }
+    float4 bs1 = bounding_sphere<NV>(D1[0], D1[1], D1[2], l, gm);
+    float4 bs2 = bounding_sphere<NV>(D2[0], D2[1], D2[2], l, gm);
+    if (l == 0) {
+        // spring_length *= 1/2 - radius/(n_vertices*spring_length)   (bit-exact op order)
+        const float L = gs.z;
+        const float div_factor = __fsub_rn(0.5f, __fdiv_rn(pot.radius, __fmul_rn((float)NV, L)));
+        const float newL = __fmul_rn(div_factor, L);
+        const float g1 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 0, d.seed, d.iteration, a, 0);
+        const float g2 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 1, d.seed, d.iteration, a, 0);
+        const float l1 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 0, d.seed, d.iteration, a, 1);
+        const float l2 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 1, d.seed, d.iteration, a, 1);
+        d.grow[a] = make_float4(g1, l1, newL, 0.f);
+        d.grow[b] = make_float4(g2, l2, newL, 0.f);
+        d.pot[b] = pot;
+        d.mech[b] = d.mech[a];
+        d.cyc[b] = cp;
+        d.nn[b] = d.nn[a];
+        d.nhist[b] = 0;
+        d.bsphere[a] = bs1;
+        d.bsphere[b] = bs2;
+        atomicMax(&d.status->emax_bits, __float_as_uint(fmaxf(bs1.w, bs2.w)));
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// launchers (dispatch on n_vertices)
+#define CRM_NV_LIST(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
+
+static inline unsigned blocks_for(uint64_t threads, unsigned bs) { return (unsigned)((threads + bs - 1) / bs); }
+
+bool nv_supported(int nv) { return nv >= 2 && nv <= 16; }
+int lanes_per_rod(int nv) { return pow2ceil(nv); }
+
+void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st) {
+    if (n == 0) return;
+#define X(NVV) if (nv == NVV) k_unpack<NVV><<<blocks_for((uint64_t)n * 3 * Lay<NVV>::LP, 256), 256, 0, st>>>(src, dst, n);
+    CRM_NV_LIST(X)
+#undef X
+}
+void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st) {
+    if (n == 0) return;
+#define X(NVV) if (nv == NVV) k_pack<NVV><<<blocks_for((uint64_t)n * 3 * NVV, 256), 256, 0, st>>>(src, dst, n);
+    CRM_NV_LIST(X)
+#undef X
+}
+void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st) {
+    if (d.n == 0) return;
+#define X(NVV) if (nv == NVV) k_bounds<NVV><<<blocks_for((uint64_t)d.n * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
+    CRM_NV_LIST(X)
+#undef X
+}
+int launch_binning(const Dev& d, cudaStream_t st) {
+    if (d.n == 0) return 0;
+    uint32_t ncells = (uint32_t)d.ncx * (uint32_t)d.ncy;
+    cudaMemsetAsync(d.cell_count, 0, sizeof(uint32_t) * ncells, st);
+    k_bin_count<<<blocks_for(d.n, 256), 256, 0, st>>>(d);
+    k_bin_scan<<<1, 1024, 0, st>>>(d, ncells);
+    k_bin_scatter<<<blocks_for(d.n, 256), 256, 0, st>>>(d);
+    k_bin_sort<<<blocks_for(ncells, 128), 128, 0, st>>>(d, ncells);
+    return 4;
+}
+void launch_force(int nv, const Dev& d, bool fast, bool count, cudaStream_t st) {
+    if (d.n == 0) return;
+#define X(NVV)                                                                              \
+    if (nv == NVV) {                                                                        \
+        unsigned nb = blocks_for((uint64_t)d.n * Lay<NVV>::LP, 128);                        \
+        if (count) {                                                                        \
+            if (fast) k_force<NVV, true, true><<<nb, 128, 0, st>>>(d);                      \
+            else k_force<NVV, false, true><<<nb, 128, 0, st>>>(d);                          \
+        } else {                                                                            \
+            if (fast) k_force<NVV, true, false><<<nb, 128, 0, st>>>(d);                     \
+            else k_force<NVV, false, false><<<nb, 128, 0, st>>>(d);                         \
+        }                                                                                   \
+    }
+    CRM_NV_LIST(X)
+#undef X
+}
+void launch_integrate(int nv, const Dev& d, cudaStream_t st) {
+    if (d.n == 0) return;
+#define X(NVV) if (nv == NVV) k_integrate<NVV><<<blocks_for((uint64_t)d.n * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
+    CRM_NV_LIST(X)
+#undef X
+}
+void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st) {
+    if (n_div == 0) return;
+#define X(NVV) if (nv == NVV) k_divide<NVV><<<blocks_for((uint64_t)n_div * Lay<NVV>::LP, 128), 128, 0, st>>>(d, n_div, n0);
+    CRM_NV_LIST(X)
+#undef X
+}
+
+}  // namespace crm
