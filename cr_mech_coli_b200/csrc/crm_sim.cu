@@ -1,0 +1,624 @@
+// crm_sim.cu — host orchestration of the colony-mechanics path + the C ABI of
+// include/crm_b200.h.  Replaces the run_main! driver of the reference
+// (src/simulation.rs:234-319): save schedule, per-step kernel sequence, division
+// bookkeeping (CellIdentifier / parent assignment), snapshots.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "crm_device.cuh"
+
+namespace crm {
+// launchers (crm_kernels.cu)
+bool nv_supported(int nv);
+int lanes_per_rod(int nv);
+void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
+void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
+void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
+int launch_binning(const Dev& d, cudaStream_t st);
+void launch_force(int nv, const Dev& d, bool fast, bool count, cudaStream_t st);
+void launch_integrate(int nv, const Dev& d, cudaStream_t st);
+void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st);
+// host helpers (crm_host.cpp)
+int build_save_schedule(const crm_config* c, std::vector<uint64_t>& out, uint64_t& max_iter, std::string& err);
+}  // namespace crm
+
+using namespace crm;
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                               \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(CRM_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),  \
+                        __FILE__, __LINE__);                                                   \
+    } while (0)
+
+struct HostSnap {
+    uint64_t iteration;
+    uint32_t n;
+    std::vector<float> pos, vel;
+    std::vector<crm_rod_params> par;
+    std::vector<crm_ident> ids, parents;
+};
+
+struct crm_sim {
+    crm_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int nv = 0, lp = 0;
+    uint32_t n = 0, cap = 0;
+    uint32_t ncells_cap = 0;
+    Dev d{};
+    float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
+    Status* h_status = nullptr;  // pinned
+    float emax = 0.0f;
+    float rsearch = 0.0f;
+    bool fast_math = true;
+    // host-side bookkeeping
+    std::vector<crm_rod_params> base;  // cold fields per slot
+    std::vector<crm_ident> ids, parents;
+    std::vector<uint64_t> vox_counter;
+    std::vector<DivRecord> h_div;
+    uint64_t iteration = 0, rod_steps = 0, launches = 0;
+    std::vector<uint64_t> save_iter;
+    uint64_t max_iter = 0;
+    std::vector<HostSnap> snaps;
+    // timers
+    bool timers = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double force_ms = 0.0;
+    uint64_t force_launches = 0;
+    uint64_t last_pairs_cut = 0, last_pairs_tested = 0;
+};
+
+template <class T>
+static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st) {
+    T* np_ = nullptr;
+    CK(cudaMalloc(&np_, sizeof(T) * new_count));
+    CK(cudaMemsetAsync(np_, 0, sizeof(T) * new_count, st));
+    if (ptr && old_count) CK(cudaMemcpyAsync(np_, ptr, sizeof(T) * old_count, cudaMemcpyDeviceToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    if (ptr) CK(cudaFree(ptr));
+    ptr = np_;
+    return 0;
+}
+
+// grow every per-rod array to `need` slots, preserving the first s->n
+static int reserve(crm_sim* s, uint32_t need) {
+    if (need <= s->cap) return 0;
+    uint32_t cap = s->cap ? s->cap : 1024;
+    while (cap < need) cap *= 2;
+    const size_t st_ = (size_t)3 * s->lp;
+    const size_t on = s->n, oc = (size_t)s->n * st_;
+    int rc;
+#define G(p, cnt_old, cnt_new) if ((rc = regrow(p, cnt_old, cnt_new, s->stream))) return rc
+    G(s->d.pos, oc, cap * st_);
+    G(s->d.vel, oc, cap * st_);
+    G(s->d.force, oc, cap * st_);
+    G(s->d.dx1, oc, cap * st_);
+    G(s->d.dv1, oc, cap * st_);
+    G(s->d.dx2, oc, cap * st_);
+    G(s->d.dv2, oc, cap * st_);
+    G(s->d.nhist, on, (size_t)cap);
+    G(s->d.pot, on, (size_t)cap);
+    G(s->d.mech, on, (size_t)cap);
+    G(s->d.grow, on, (size_t)cap);
+    G(s->d.cyc, on, (size_t)cap);
+    G(s->d.nn, on, (size_t)cap);
+    G(s->d.bsphere, on, (size_t)cap);
+    G(s->d.cell_of, 0, (size_t)cap);
+    G(s->d.cell_rank, 0, (size_t)cap);
+    G(s->d.sorted, 0, (size_t)cap);
+    G(s->d.divlist, 0, (size_t)cap);
+    G(s->stage, 0, (size_t)cap * s->nv * 3);
+#undef G
+    s->d.divcap = cap;
+    s->cap = cap;
+    return 0;
+}
+
+static int reserve_cells(crm_sim* s, uint32_t ncells) {
+    if (ncells + 1 <= s->ncells_cap) return 0;
+    uint32_t c = s->ncells_cap ? s->ncells_cap : 4096;
+    while (c < ncells + 1) c *= 2;
+    if (s->d.cell_start) CK(cudaFree(s->d.cell_start));
+    if (s->d.cell_count) CK(cudaFree(s->d.cell_count));
+    CK(cudaMalloc(&s->d.cell_start, sizeof(uint32_t) * c));
+    CK(cudaMalloc(&s->d.cell_count, sizeof(uint32_t) * c));
+    s->ncells_cap = c;
+    return 0;
+}
+
+// Centroid cell list geometry: the 3x3 stencil is complete when the cell edge is at
+// least 2*max_extent + search radius.
+static int configure_grid(crm_sim* s) {
+    const float h = (2.0f * s->emax + s->rsearch) * 1.0005f + 1e-4f;
+    double ncx = std::floor((double)s->cfg.domain_size[0] / h), ncy = std::floor((double)s->cfg.domain_size[1] / h);
+    if (!(ncx >= 1.0)) ncx = 1.0;
+    if (!(ncy >= 1.0)) ncy = 1.0;
+    const double MAXC = 4.0 * 1024 * 1024;
+    while (ncx * ncy > MAXC) {
+        ncx = std::max(1.0, std::floor(ncx / 1.5));
+        ncy = std::max(1.0, std::floor(ncy / 1.5));
+    }
+    s->d.ncx = (int)ncx;
+    s->d.ncy = (int)ncy;
+    s->d.inv_wx = (float)(ncx / (double)s->cfg.domain_size[0]);
+    s->d.inv_wy = (float)(ncy / (double)s->cfg.domain_size[1]);
+    return reserve_cells(s, (uint32_t)(ncx * ncy));
+}
+
+// ------------------------------------------------------------------------------------
+// Largest f32 x with sqrtf(x) <= cutoff: lets the kernel test the reference's `r > cutoff`
+// on r^2 without changing a single outcome.
+static float cutoff_threshold(float c) {
+    if (!(c >= 0.0f) || !std::isfinite(c)) return c >= 0.0f ? INFINITY : -1.0f;
+    float x = c * c;
+    while (x > 0.0f && std::sqrt(x) > c) x = std::nextafter(x, 0.0f);
+    while (std::sqrt(std::nextafter(x, INFINITY)) <= c) x = std::nextafter(x, INFINITY);
+    return x;
+}
+
+static void fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams& mech, GrowState& grow,
+                               CycleParams& cyc) {
+    pot.type = p.potential;
+    pot.radius = p.radius;
+    pot.cutoff2 = cutoff_threshold(p.cutoff);
+    if (p.potential == CRM_POT_MORSE) {
+        pot.strength = p.strength;
+        pot.a = p.potential_stiffness;
+        pot.b = pot.c = pot.d = 0.0f;
+    } else {
+        // same f32 operation order as the reference's `strength * mie_constant * part`
+        const float en = p.en, em = p.em;
+        const float C = en / (en - em) * powf(en / em, en / (en - em));
+        pot.strength = p.strength * C;
+        pot.a = p.bound;
+        pot.b = en;
+        pot.c = em;
+        pot.d = powf(em / en, 1.0f / (en - em));
+    }
+    mech = make_float4(p.spring_tension, p.rigidity, p.damping, p.diffusion_constant);
+    grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, 0.0f);
+    memset(&cyc, 0, sizeof(cyc));
+    cyc.growth_kind = p.growth_setter_kind;
+    cyc.growth_a = p.growth_setter_a;
+    cyc.growth_b = p.growth_setter_b;
+    cyc.thr_kind = p.threshold_setter_kind;
+    cyc.thr_a = p.threshold_setter_a;
+    cyc.thr_b = p.threshold_setter_b;
+    cyc.has_nr = p.has_neighbor_reduction;
+    cyc.nr_max = p.neighbor_reduction_max;
+    cyc.nr_exp = p.neighbor_reduction_exp;
+}
+
+static int read_status(crm_sim* s) {
+    CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    return 0;
+}
+
+static int report_device_error(crm_sim* s) {
+    const Status& st = *s->h_status;
+    if (st.err_code == 0) return 0;
+    std::vector<float> rod((size_t)3 * s->lp);
+    cudaMemcpy(rod.data(), s->d.pos + (size_t)st.err_slot * 3 * s->lp, sizeof(float) * rod.size(),
+               cudaMemcpyDeviceToHost);
+    std::string dump;
+    char tmp[64];
+    for (int c = 0; c < 3; ++c)
+        for (int i = 0; i < s->nv; ++i) {
+            snprintf(tmp, sizeof(tmp), "%s%g", dump.empty() ? "" : ", ", rod[c * s->lp + i]);
+            dump += tmp;
+        }
+    if (st.err_code == CRM_ERR_BOUNDARY)
+        return fail(CRM_ERR_BOUNDARY, "BoundaryError: Particle is out of domain at pos [%s] (rod slot %u, iteration %llu)",
+                    dump.c_str(), st.err_slot, (unsigned long long)s->iteration);
+    return fail(CRM_ERR_NUMERIC, "CalcError: non-finite position [%s] (rod slot %u, iteration %llu)", dump.c_str(),
+                st.err_slot, (unsigned long long)s->iteration);
+}
+
+// Divisions of this step: order the mothers by slot, run the geometry kernel, then do the
+// identifier bookkeeping of the backend's update_cell_cycle_4 on the host (mothers are renamed
+// first, then the new cells, with the per-voxel pre-incremented counter).
+static int handle_divisions(crm_sim* s, uint32_t n_div) {
+    const uint32_t n0 = s->n;
+    s->h_div.resize(n_div);
+    CK(cudaMemcpyAsync(s->h_div.data(), s->d.divlist, sizeof(DivRecord) * n_div, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    std::sort(s->h_div.begin(), s->h_div.end(), [](const DivRecord& a, const DivRecord& b) { return a.slot < b.slot; });
+    for (uint32_t r = 0; r < n_div; ++r) {
+        const crm_rod_params& p = s->base[s->h_div[r].slot];
+        if (!(p.radius > 0.0f))
+            return fail(CRM_ERR_DIVISION, "DivisionError: cannot divide rod slot %u (radius %g)", s->h_div[r].slot, p.radius);
+    }
+    int rc = reserve(s, n0 + n_div);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
+    s->d.n = n0;
+    launch_divide(s->nv, s->d, n_div, n0, s->stream);
+    s->launches += 1;
+    CK(cudaGetLastError());
+    if ((rc = read_status(s))) return rc;
+    if ((rc = report_device_error(s))) return rc;
+    // identifiers
+    const uint32_t nvox = s->cfg.n_voxels[0] * s->cfg.n_voxels[1];
+    std::vector<uint32_t> per_vox(nvox, 0), rank_vox(nvox, 0);
+    for (uint32_t r = 0; r < n_div; ++r) per_vox[s->h_div[r].uvox]++;
+    s->base.resize(n0 + n_div);
+    s->ids.resize(n0 + n_div);
+    s->parents.resize(n0 + n_div);
+    for (uint32_t r = 0; r < n_div; ++r) {
+        const uint32_t a = s->h_div[r].slot, b = n0 + r, v = s->h_div[r].uvox;
+        const crm_ident mother = s->ids[a];
+        const uint32_t k = rank_vox[v]++;
+        s->ids[a] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + 1 + k};
+        s->parents[a] = mother;
+        s->ids[b] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + per_vox[v] + 1 + k};
+        s->parents[b] = mother;
+        s->base[b] = s->base[a];
+    }
+    for (uint32_t v = 0; v < nvox; ++v) s->vox_counter[v] += 2ull * per_vox[v];
+    s->n = n0 + n_div;
+    s->d.n = s->n;
+    return 0;
+}
+
+static int launch_neighbour_and_force(crm_sim* s, bool count) {
+    int rc = configure_grid(s);
+    if (rc) return rc;
+    s->d.n = s->n;
+    s->d.rsearch = s->rsearch;
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    s->launches += launch_binning(s->d, s->stream);
+    if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
+    launch_force(s->nv, s->d, s->fast_math, count, s->stream);
+    if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
+    s->launches += 1;
+    return 0;
+}
+
+static int step_once(crm_sim* s) {
+    if (s->n == 0) {
+        s->iteration += 1;
+        return 0;
+    }
+    s->iteration += 1;
+    s->rod_steps += s->n;
+    s->d.iteration = s->iteration;
+    int rc = launch_neighbour_and_force(s, false);
+    if (rc) return rc;
+    launch_integrate(s->nv, s->d, s->stream);
+    s->launches += 1;
+    CK(cudaGetLastError());
+    if ((rc = read_status(s))) return rc;
+    if (s->timers) {
+        float ms = 0.0f;
+        CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        s->force_ms += ms;
+        s->force_launches += 1;
+    }
+    if ((rc = report_device_error(s))) return rc;
+    s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    const uint32_t n_div = s->h_status->n_div;
+    if (n_div) {
+        if ((rc = handle_divisions(s, n_div))) return rc;
+        s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    }
+    return 0;
+}
+
+static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
+    const size_t m = (size_t)s->n * s->nv * 3;
+    if (s->n == 0) return 0;
+    if (pos) {
+        launch_pack(s->nv, s->d.pos, s->stage, s->n, s->stream);
+        CK(cudaMemcpyAsync(pos, s->stage, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    if (vel) {
+        launch_pack(s->nv, s->d.vel, s->stage, s->n, s->stream);
+        CK(cudaMemcpyAsync(vel, s->stage, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    if (par) {
+        std::vector<GrowState> g(s->n);
+        std::vector<uint32_t> nn(s->n);
+        CK(cudaMemcpyAsync(g.data(), s->d.grow, sizeof(GrowState) * s->n, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(nn.data(), s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        for (uint32_t a = 0; a < s->n; ++a) {
+            par[a] = s->base[a];
+            par[a].growth_rate = g[a].x;
+            par[a].spring_length_threshold = g[a].y;
+            par[a].spring_length = g[a].z;
+            par[a].n_neighbors = nn[a];
+        }
+    }
+    return 0;
+}
+
+static int take_snapshot(crm_sim* s) {
+    s->snaps.emplace_back();
+    HostSnap& sn = s->snaps.back();
+    sn.iteration = s->iteration;
+    sn.n = s->n;
+    const size_t m = (size_t)s->n * s->nv * 3;
+    sn.pos.resize(m);
+    sn.vel.resize(m);
+    sn.par.resize(s->n);
+    sn.ids.assign(s->ids.begin(), s->ids.begin() + s->n);
+    sn.parents.assign(s->parents.begin(), s->parents.begin() + s->n);
+    return download_state(s, sn.pos.data(), sn.vel.data(), sn.par.data());
+}
+
+// ====================================================================================
+// C ABI
+extern "C" {
+
+int crm_abi_version(void) { return CRM_ABI_VERSION; }
+const char* crm_last_error(void) { return g_err.c_str(); }
+
+int crm_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        fail(CRM_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        return -1;
+    }
+    return n;
+}
+
+int crm_save_schedule(const crm_config* config, uint64_t* out, uint32_t cap, uint64_t* n_iterations) {
+    std::vector<uint64_t> it;
+    uint64_t mx = 0;
+    std::string err;
+    int rc = build_save_schedule(config, it, mx, err);
+    if (rc) return fail(rc, "%s", err.c_str());
+    for (size_t i = 0; i < it.size() && i < cap; ++i) out[i] = it[i];
+    if (n_iterations) *n_iterations = mx;
+    return (int)it.size();
+}
+
+int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
+    if (!c || !out) return fail(CRM_ERR_INVALID, "null argument");
+    if (c->n_voxels[0] == 0 || c->n_voxels[1] == 0 || !(c->domain_size[0] > 0) || !(c->domain_size[1] > 0) ||
+        !(c->domain_height > 0))
+        return fail(CRM_ERR_INVALID, "invalid domain configuration");
+    std::vector<uint64_t> it;
+    uint64_t mx = 0;
+    std::string err;
+    int rc = build_save_schedule(c, it, mx, err);
+    if (rc) return fail(rc, "%s", err.c_str());
+    int ndev = crm_device_count();
+    if (ndev <= 0) return fail(CRM_ERR_CUDA, "no CUDA device available (cr_mech_coli_b200 has no CPU fallback): %s", g_err.c_str());
+    if (device < 0 || device >= ndev) return fail(CRM_ERR_INVALID, "device %d out of range (%d visible)", device, ndev);
+    CK(cudaSetDevice(device));
+    crm_sim* s = new crm_sim();
+    s->cfg = *c;
+    s->device = device;
+    s->save_iter = it;
+    s->max_iter = mx;
+    s->vox_counter.assign((size_t)c->n_voxels[0] * c->n_voxels[1], 0);
+    const char* ex = getenv("CRM_B200_EXACT_MATH");
+    s->fast_math = !(ex && ex[0] == '1');
+    CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CK(cudaMalloc(&s->d.status, sizeof(Status)));
+    CK(cudaMemset(s->d.status, 0, sizeof(Status)));
+    CK(cudaMallocHost(&s->h_status, sizeof(Status)));
+    CK(cudaEventCreate(&s->ev0));
+    CK(cudaEventCreate(&s->ev1));
+    s->d.lx = c->domain_size[0];
+    s->d.ly = c->domain_size[1];
+    s->d.lz = c->domain_height;
+    s->d.unx = (int)c->n_voxels[0];
+    s->d.uny = (int)c->n_voxels[1];
+    s->d.uvx_w = c->domain_size[0] / (float)c->n_voxels[0];
+    s->d.uvy_w = c->domain_size[1] / (float)c->n_voxels[1];
+    s->d.gel_pressure = c->gel_pressure;
+    s->d.surface_friction = c->surface_friction;
+    s->d.surface_friction_distance = c->surface_friction_distance;
+    s->d.dt = c->dt;
+    s->d.seed = c->rng_seed;
+    *out = s;
+    return 0;
+}
+
+void crm_sim_destroy(crm_sim* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
+                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.cell_of, s->d.cell_rank,
+                    s->d.cell_start, s->d.cell_count, s->d.sorted, s->d.divlist, s->d.status, s->stage};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (s->h_status) cudaFreeHost(s->h_status);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int crm_sim_set_exact_math(crm_sim* s, int exact) {
+    s->fast_math = !exact;
+    return 0;
+}
+
+int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm_rod_params* par, uint32_t n,
+                       uint32_t nv) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    if (!nv_supported((int)nv)) return fail(CRM_ERR_INVALID, "n_vertices=%u unsupported (2..16)", nv);
+    if (s->nv != 0 && s->nv != (int)nv) return fail(CRM_ERR_INVALID, "n_vertices cannot change on a live sim");
+    CK(cudaSetDevice(s->device));
+    s->nv = (int)nv;
+    s->lp = lanes_per_rod((int)nv);
+    s->n = 0;
+    int rc = reserve(s, std::max<uint32_t>(n + n / 2 + 16, 1024));
+    if (rc) return rc;
+    s->iteration = 0;
+    s->snaps.clear();
+    std::fill(s->vox_counter.begin(), s->vox_counter.end(), 0);
+    s->base.assign(par, par + n);
+    s->ids.resize(n);
+    s->parents.resize(n);
+    std::vector<PotParams> pot(n);
+    std::vector<MechParams> mech(n);
+    std::vector<GrowState> grow(n);
+    std::vector<CycleParams> cyc(n);
+    std::vector<uint32_t> nn(n);
+    float rmax = 0.0f, cmax = 0.0f;
+    for (uint32_t a = 0; a < n; ++a) {
+        s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, a};
+        s->parents[a] = crm_ident{-1, 0, 0};
+        if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE)
+            return fail(CRM_ERR_INVALID, "rod %u: unknown potential %d", a, par[a].potential);
+        fill_device_params(par[a], pot[a], mech[a], grow[a], cyc[a]);
+        nn[a] = par[a].n_neighbors;
+        rmax = std::max(rmax, par[a].radius);
+        cmax = std::max(cmax, par[a].cutoff);
+    }
+    s->rsearch = std::max(cmax, 2.0f * rmax * 0.70710678f) * 1.0001f;
+    const size_t m = (size_t)n * nv * 3;
+    if (n) {
+        CK(cudaMemcpyAsync(s->stage, pos, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
+        launch_unpack(s->nv, s->stage, s->d.pos, n, s->stream);
+        CK(cudaStreamSynchronize(s->stream));
+        CK(cudaMemcpyAsync(s->stage, vel, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
+        launch_unpack(s->nv, s->stage, s->d.vel, n, s->stream);
+        CK(cudaMemcpyAsync(s->d.pot, pot.data(), sizeof(PotParams) * n, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.mech, mech.data(), sizeof(MechParams) * n, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.grow, grow.data(), sizeof(GrowState) * n, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.cyc, cyc.data(), sizeof(CycleParams) * n, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.nn, nn.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemsetAsync(s->d.nhist, 0, n, s->stream));
+        CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+        s->n = n;
+        s->d.n = n;
+        launch_bounds_kernel(s->nv, s->d, s->stream);
+        s->launches += 3;
+        CK(cudaGetLastError());
+        if ((rc = read_status(s))) return rc;
+        s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+        if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite initial positions");
+    }
+    return 0;
+}
+
+int crm_sim_step(crm_sim* s, uint32_t n_steps) {
+    CK(cudaSetDevice(s->device));
+    for (uint32_t k = 0; k < n_steps; ++k) {
+        int rc = step_once(s);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int crm_sim_run(crm_sim* s) {
+    CK(cudaSetDevice(s->device));
+    size_t next = 0;
+    int rc;
+    while (next < s->save_iter.size() && s->save_iter[next] < s->iteration) next++;
+    if (next < s->save_iter.size() && s->save_iter[next] == s->iteration) {
+        if ((rc = take_snapshot(s))) return rc;
+        next++;
+    }
+    while (s->iteration < s->max_iter) {
+        if ((rc = step_once(s))) return rc;
+        while (next < s->save_iter.size() && s->save_iter[next] < s->iteration) next++;
+        if (next < s->save_iter.size() && s->save_iter[next] == s->iteration) {
+            if ((rc = take_snapshot(s))) return rc;
+            next++;
+        }
+    }
+    return 0;
+}
+
+int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
+    CK(cudaSetDevice(s->device));
+    if (s->n == 0) return 0;
+    int rc = launch_neighbour_and_force(s, true);
+    if (rc) return rc;
+    CK(cudaGetLastError());
+    if ((rc = read_status(s))) return rc;
+    s->last_pairs_cut = s->h_status->pairs_in_cutoff;
+    s->last_pairs_tested = s->h_status->pairs_tested;
+    if (out_force) {
+        launch_pack(s->nv, s->d.force, s->stage, s->n, s->stream);
+        CK(cudaMemcpyAsync(out_force, s->stage, sizeof(float) * (size_t)s->n * s->nv * 3, cudaMemcpyDeviceToHost, s->stream));
+    }
+    if (out_nn) CK(cudaMemcpyAsync(out_nn, s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    return 0;
+}
+
+uint32_t crm_sim_n_rods(const crm_sim* s) { return s->n; }
+uint32_t crm_sim_n_vertices(const crm_sim* s) { return (uint32_t)s->nv; }
+uint64_t crm_sim_iteration(const crm_sim* s) { return s->iteration; }
+uint64_t crm_sim_launch_count(const crm_sim* s) { return s->launches; }
+uint64_t crm_sim_rod_steps(const crm_sim* s) { return s->rod_steps; }
+
+int crm_sim_get_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par, crm_ident* ids, crm_ident* parents) {
+    CK(cudaSetDevice(s->device));
+    int rc = download_state(s, pos, vel, par);
+    if (rc) return rc;
+    if (ids) memcpy(ids, s->ids.data(), sizeof(crm_ident) * s->n);
+    if (parents) memcpy(parents, s->parents.data(), sizeof(crm_ident) * s->n);
+    return 0;
+}
+
+uint32_t crm_sim_n_snapshots(const crm_sim* s) { return (uint32_t)s->snaps.size(); }
+
+int crm_sim_snapshot_info(const crm_sim* s, uint32_t k, uint64_t* iteration, uint32_t* n_rods) {
+    if (k >= s->snaps.size()) return fail(CRM_ERR_INVALID, "snapshot %u out of range", k);
+    if (iteration) *iteration = s->snaps[k].iteration;
+    if (n_rods) *n_rods = s->snaps[k].n;
+    return 0;
+}
+
+int crm_sim_snapshot_copy(const crm_sim* s, uint32_t k, float* pos, float* vel, crm_rod_params* par, crm_ident* ids,
+                          crm_ident* parents) {
+    if (k >= s->snaps.size()) return fail(CRM_ERR_INVALID, "snapshot %u out of range", k);
+    const HostSnap& sn = s->snaps[k];
+    if (pos) memcpy(pos, sn.pos.data(), sizeof(float) * sn.pos.size());
+    if (vel) memcpy(vel, sn.vel.data(), sizeof(float) * sn.vel.size());
+    if (par) memcpy(par, sn.par.data(), sizeof(crm_rod_params) * sn.n);
+    if (ids) memcpy(ids, sn.ids.data(), sizeof(crm_ident) * sn.n);
+    if (parents) memcpy(parents, sn.parents.data(), sizeof(crm_ident) * sn.n);
+    return 0;
+}
+
+int crm_sim_enable_timers(crm_sim* s, int enable) {
+    s->timers = enable != 0;
+    s->force_ms = 0.0;
+    s->force_launches = 0;
+    return 0;
+}
+
+int crm_sim_read_timers(crm_sim* s, double* force_ms, uint64_t* force_launches, uint64_t* pairs_cut,
+                        uint64_t* pairs_tested) {
+    if (force_ms) *force_ms = s->force_ms;
+    if (force_launches) *force_launches = s->force_launches;
+    if (pairs_cut) *pairs_cut = s->last_pairs_cut;
+    if (pairs_tested) *pairs_tested = s->last_pairs_tested;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,129 @@
+"""Synthetic colonies and parameter blocks shared by tests, bench.py and smoke().
+
+The layouts follow SURVEY.md §8(d): a jittered nematic lattice of straight rods
+(C3 headline workload) and helper constructors for the ``crm_rod_params`` records
+with the reference's defaults (reference src/config.rs:128-140,243-274).
+"""
+
+from __future__ import annotations
+
+import numpy as np
+
+from ._capi import POT_MIE, POT_MORSE, ROD_PARAMS_DTYPE, SETTER_EXPLICIT, SETTER_NORMAL
+
+
+def base_params(n: int) -> np.ndarray:
+    p = np.zeros(n, dtype=ROD_PARAMS_DTYPE)
+    p["diffusion_constant"] = 0.0
+    p["spring_tension"] = 1.0
+    p["rigidity"] = 2.0
+    p["spring_length"] = 3.0
+    p["damping"] = 1.0
+    p["growth_rate"] = 0.01
+    p["growth_setter_kind"] = SETTER_NORMAL
+    p["growth_setter_a"] = 0.01
+    p["growth_setter_b"] = 0.0
+    p["spring_length_threshold"] = 6.0
+    p["threshold_setter_kind"] = SETTER_EXPLICIT
+    p["threshold_setter_a"] = 6.0
+    p["threshold_setter_b"] = 6.0
+    return p
+
+
+def morse_params(n: int, radius=3.0, potential_stiffness=0.5, cutoff=10.0, strength=0.1, **kw) -> np.ndarray:
+    """AgentSettings() defaults: Morse(radius=3, stiffness=0.5, cutoff=10, strength=0.1)."""
+    p = base_params(n)
+    p["potential"] = POT_MORSE
+    p["radius"] = radius
+    p["potential_stiffness"] = potential_stiffness
+    p["cutoff"] = cutoff
+    p["strength"] = strength
+    _apply(p, kw)
+    return p
+
+
+def mie_params(n: int, radius=1.5, strength=0.1, bound=100.0, cutoff=6.0, en=6.0, em=3.0, **kw) -> np.ndarray:
+    """C3 headline parameters: Mie n=6, m=3, r=1.5, cutoff 6, bound 100."""
+    p = base_params(n)
+    p["potential"] = POT_MIE
+    p["radius"] = radius
+    p["strength"] = strength
+    p["bound"] = bound
+    p["cutoff"] = cutoff
+    p["en"] = en
+    p["em"] = em
+    _apply(p, kw)
+    return p
+
+
+def _apply(p, kw):
+    for k, v in kw.items():
+        if k == "growth_rate":
+            p["growth_rate"] = v
+            p["growth_setter_a"] = v
+        elif k == "neighbor_reduction":
+            if v is None:
+                p["has_neighbor_reduction"] = 0
+            else:
+                p["has_neighbor_reduction"] = 1
+                p["neighbor_reduction_max"] = v[0]
+                p["neighbor_reduction_exp"] = v[1]
+        else:
+            p[k] = v
+
+
+def lattice_colony(n_rods: int, domain: float | None = None, n_vertices: int = 8, spring_length: float = 3.0,
+                   spacing=(24.0, 4.0), angle_std: float = 0.1, jitter: float = 0.3, seed: int = 12345,
+                   z: float = 1.25, z_jitter: float = 0.0, margin: float = 14.0):
+    """Jittered nematic lattice (C3): rod centres on a (spacing_x, spacing_y) lattice, angle ~
+    N(0, angle_std), uniform jitter; returns pos[n_rods, n_vertices, 3] f32.  If ``domain`` is
+    given the lattice is cut to fit a square domain of that edge (with ``margin``)."""
+    rng = np.random.default_rng(seed)
+    sx, sy = spacing
+    if domain is None:
+        ny = int(np.ceil(np.sqrt(n_rods * sx / sy)))
+        nx = int(np.ceil(n_rods / ny))
+    else:
+        nx = max(1, int((domain - 2 * margin) // sx))
+        ny = max(1, int((domain - 2 * margin) // sy))
+        if nx * ny < n_rods:
+            raise ValueError(f"domain {domain} holds only {nx * ny} rods at spacing {spacing}")
+        ny = min(ny, int(np.ceil(np.sqrt(n_rods * sx / sy))))
+        nx = int(np.ceil(n_rods / ny))
+    idx = np.arange(n_rods)
+    cx = margin + (idx // ny) * sx + rng.uniform(-jitter, jitter, n_rods)
+    cy = margin + (idx % ny) * sy + rng.uniform(-jitter, jitter, n_rods)
+    cz = z + rng.uniform(-z_jitter, z_jitter, n_rods) if z_jitter else np.full(n_rods, z)
+    ang = rng.normal(0.0, angle_std, n_rods)
+    t = (np.arange(n_vertices) - (n_vertices - 1) / 2.0) * spring_length
+    pos = np.empty((n_rods, n_vertices, 3), dtype=np.float32)
+    pos[:, :, 0] = cx[:, None] + t[None, :] * np.cos(ang)[:, None]
+    pos[:, :, 1] = cy[:, None] + t[None, :] * np.sin(ang)[:, None]
+    pos[:, :, 2] = cz[:, None]
+    return pos
+
+
+def lattice_domain(n_rods: int, spacing=(24.0, 4.0), margin: float = 14.0) -> float:
+    """Edge of the square domain that holds ``lattice_colony(n_rods)``."""
+    sx, sy = spacing
+    ny = int(np.ceil(np.sqrt(n_rods * sx / sy)))
+    nx = int(np.ceil(n_rods / ny))
+    return float(max(nx * sx, ny * sy) + 2 * margin)
+
+
+def random_colony(n_rods: int, domain: float, n_vertices: int = 8, spring_length: float = 3.0, seed: int = 0,
+                  height: float = 2.5, bend: float = 0.05, z_spread: float = 0.2):
+    """Randomly placed and oriented, slightly bent rods (dense overlaps allowed): a stress case
+    for the neighbour search and the force kernel."""
+    rng = np.random.default_rng(seed)
+    half = (n_vertices - 1) * spring_length / 2 + 1.0
+    c = rng.uniform(half, domain - half, (n_rods, 2))
+    ang = rng.uniform(0, 2 * np.pi, n_rods)
+    pos = np.empty((n_rods, n_vertices, 3), dtype=np.float32)
+    t = (np.arange(n_vertices) - (n_vertices - 1) / 2.0) * spring_length
+    curv = rng.normal(0, bend, n_rods)
+    a = ang[:, None] + curv[:, None] * t[None, :] / spring_length
+    pos[:, :, 0] = c[:, 0:1] + t[None, :] * np.cos(a)
+    pos[:, :, 1] = c[:, 1:2] + t[None, :] * np.sin(a)
+    pos[:, :, 2] = height * (0.5 + rng.uniform(-z_spread, z_spread, (n_rods, 1))) + rng.normal(0, 0.01, (n_rods, n_vertices))
+    return pos

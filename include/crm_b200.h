@@ -157,6 +157,10 @@ int crm_sim_step(crm_sim* sim, uint32_t n_steps);
  * out_force: [n_rods][n_vertices][3]; out_n_neighbors: [n_rods] (either may be NULL). */
 int crm_sim_compute_forces(crm_sim* sim, float* out_force, uint32_t* out_n_neighbors);
 
+/* 1: IEEE sqrt/div + libdevice expf/powf in the force kernel; 0 (default): MUFU
+ * approximations (rsqrt/ex2/lg2/rcp).  Env CRM_B200_EXACT_MATH=1 sets the default. */
+int crm_sim_set_exact_math(crm_sim* sim, int exact);
+
 uint32_t crm_sim_n_rods(const crm_sim* sim);
 uint32_t crm_sim_n_vertices(const crm_sim* sim);
 uint64_t crm_sim_iteration(const crm_sim* sim);
