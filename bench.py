@@ -1,0 +1,301 @@
+#!/usr/bin/env python
+"""bench.py — agent-steps/s of the colony-mechanics step (BASELINE.json metric).
+
+A "step" is one mechanics step (binning, rod-rod forces, springs/bending/integrator,
+growth/division, boundary) over the whole synthetic colony.  Workload at N=1 = BASELINE.json
+configs[2]: 2D monolayer, 1e6 rods x 8 vertices, Mie potential (SURVEY.md §8d "C3").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--rods R] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` = rods*K / device time with the colony resident in
+HBM; `e2e` = the same through the C-ABI with host buffers (upload + K steps + download in the
+timed region); `roofline` = the force kernel against the measured FP32 peak; `cpu_baseline` =
+the CPU oracle on a bounded sample of the same lattice.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "agent-steps/sec at 1e6 rods on 1/2/4/8 B200; ms per mechanics step"
+UNIT = "agent-steps/s"
+# algorithmic work of the force kernel (SURVEY.md §8d / DESIGN.md): one point-segment
+# evaluation = 65 FLOP (Mie) / 59 FLOP (Morse); 56 evaluations per ordered interacting pair
+FLOP_PER_EVAL = {"mie": 65.0, "morse": 59.0}
+EVALS_PER_ORDERED_PAIR = 56.0
+MECH_BYTES_PER_ROD_STEP = 836.0
+
+
+def workload(n_rods: int, seed: int = 12345):
+    from cr_mech_coli_b200 import _capi
+    from cr_mech_coli_b200.testing import lattice_colony, lattice_domain, mie_params
+
+    L = lattice_domain(n_rods)
+    nvx = max(1, int(L // 40.0))  # reference voxels: edge >= rod length + cutoff
+    cfg = _capi.make_config(domain_size=(L, L), domain_height=2.5, n_voxels=(nvx, nvx), dt=0.01, t_max=1e6,
+                            n_saves=0)
+    pos = lattice_colony(n_rods, seed=seed)
+    par = mie_params(n_rods, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    return cfg, pos, par
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.idx = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return json.loads(p.read_text()), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+def ncu_traffic():
+    """dram bytes per launch of the force kernel from the committed ncu capture (or None)."""
+    p = ROOT / "profiles" / "force_kernel_traffic.json"
+    if p.exists():
+        try:
+            return json.loads(p.read_text()).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+def cpu_baseline(n_sample: int, steps: int, threads: int | None):
+    """The CPU oracle (OpenMP over rods = the reference's rayon-over-subdomains strategy) timed on
+    a bounded sample of the same lattice."""
+    from oracle import oracle
+
+    cfg, pos, par = workload(n_sample)
+    lib = oracle.library(openmp=True)
+    if threads:
+        lib.fn("set_num_threads")(threads)
+    cores = lib.fn("num_threads")()
+    with oracle.sim(cfg, openmp=True) as o:
+        o.set_agents(pos, np.zeros_like(pos), par)
+        o.step(1)  # warm-up
+        t0 = time.perf_counter()
+        o.step(steps)
+        dt = time.perf_counter() - t0
+    return {"value": n_sample * steps / dt, "unit": UNIT, "cores": int(cores), "kind": "port",
+            "sample": f"{n_sample} rods of the same lattice x {steps} steps ({dt:.1f} s)",
+            "ms_per_step": dt / steps * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_sample = args.ref_rods
+    cb = cpu_baseline(n_sample, max(1, args.steps), None)
+    cfg_w = {"workload": "C3: 2D monolayer, jittered nematic lattice, Mie n=6 m=3, 8 vertices/rod",
+             "rods": args.rods, "dt": 0.01, "sample_rods": n_sample}
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg_w,
+            "cpu_baseline": {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port",
+                             "sample": cb["sample"]},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference = CPU restatement of the cellular_raza path (the Rust reference cannot be built "
+                    "here: no cargo, un-vendored dependency); agent-steps/s at fixed density is size-independent"}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--rods", type=int, default=1_000_000, help="rods per GPU")
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--ref-rods", type=int, default=20000)
+    ap.add_argument("--cpu-rods", type=int, default=20000)
+    ap.add_argument("--cpu-steps", type=int, default=5)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    from cr_mech_coli_b200 import _capi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group("nccl")
+        dist = dist_mod
+
+    lib = _capi.product()
+    ndev = lib.fn("device_count")()
+    if ndev <= 0:
+        raise SystemExit("bench.py needs a CUDA device: " + lib.last_error())
+    device = local_rank % ndev
+    W = max(args.warmup, 3)
+    K = args.steps
+
+    cfg, pos, par = workload(args.rods, seed=12345 + rank)
+    vel = np.zeros_like(pos)
+    n = len(pos)
+
+    # non-tensor peaks of this device (not in MEASURED_PEAKS.json)
+    import ctypes as C
+    fp32, mufu, mhz = C.c_double(0), C.c_double(0), C.c_double(0)
+    lib.check(lib.fn("microbench")(device, C.byref(fp32), C.byref(mufu), C.byref(mhz)))
+
+    def barrier():
+        if dist is not None:
+            import torch
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    sim = _capi.Sim(lib, cfg, device)
+    sim.set_agents(pos, vel, par)
+    # interacting ordered pairs of this colony (instrumented launch, outside the timed region)
+    sim.compute_forces()
+    pairs = sim.read_timers()
+    sim.step(W)
+    sim.enable_timers(True)
+    launches0 = sim.launch_count()
+    sampler = ClockSampler(device)
+    sampler.start()
+    barrier()
+    ms = sim.step_timed(K)
+    barrier()
+    clocks = sampler.stop()
+    launches = sim.launch_count() - launches0
+    tm = sim.read_timers()
+    sim.enable_timers(False)
+
+    # e2e: host buffers in, K steps, host buffers out, through the C ABI
+    sim2 = _capi.Sim(lib, cfg, device)
+    barrier()
+    t0 = time.perf_counter()
+    sim2.set_agents(pos, vel, par)
+    sim2.step(K)
+    pos_out = sim2.get_state()[0]
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    assert np.isfinite(pos_out).all()
+    h2d = pos.nbytes + vel.nbytes + n * (32 + 16 + 16 + 48 + 4)
+    d2h = pos_out.nbytes * 2 + n * 20 + K * 40
+    sim2.close()
+
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms, e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+    if rank != 0:
+        return
+
+    peaks, peaks_src = measured_peaks()
+    total_rods = n * world
+    value = total_rods * K / (ms * 1e-3)
+    force_ms = tm["force_ms"] / max(tm["force_launches"], 1)
+    flops = pairs["pairs_in_cutoff"] * EVALS_PER_ORDERED_PAIR * FLOP_PER_EVAL["mie"]
+    achieved = flops / (force_ms * 1e-3) * 1e-12 if force_ms > 0 else 0.0
+    mech_ms = ms / K - force_ms
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C3: 2D monolayer, jittered nematic lattice (24x4 um spacing), Mie n=6 m=3, "
+                               "r=1.5, cutoff 6, 8 vertices/rod, dt=0.01, growth 0",
+                   "rods_per_gpu": n, "rods_total": total_rods,
+                   "parallelism": "1 GPU" if world == 1 else f"{world} independent slabs (weak)",
+                   "l2": "state (~0.9 GB/GPU) larger than the 126 MB L2; no explicit flush",
+                   "math": "MUFU fast path (rsqrt/ex2/lg2) + bit-exact closest-point geometry"},
+        "e2e": {"value": total_rods * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d / K,
+                "d2h_bytes_per_step": d2h / K, "seconds": e2e_s},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"kernel": "k_force<8>", "bound": "fp32", "achieved": achieved, "peak": fp32.value,
+                     "unit": "TFLOP/s", "frac": achieved / fp32.value if fp32.value else None,
+                     "traffic": ncu_traffic(),
+                     "peak_source": "crm_microbench FFMA loop on this device (FP32 non-tensor peak is not in "
+                                    "MEASURED_PEAKS.json); nominal 148*128*2*1.965 GHz = 74.5",
+                     "mufu_peak_tops": mufu.value, "fma_implied_sm_mhz": mhz.value,
+                     "force_ms_per_launch": force_ms, "force_share_of_step": force_ms / (ms / K),
+                     "ordered_pairs_in_cutoff": pairs["pairs_in_cutoff"],
+                     "candidate_pairs_evaluated": pairs["pairs_tested"],
+                     "flop_per_eval": FLOP_PER_EVAL["mie"], "evals_per_ordered_pair": EVALS_PER_ORDERED_PAIR},
+        "roofline_mech": {"kernels": "binning + k_integrate (everything but the force kernel)", "bound": "hbm",
+                          "achieved": n * MECH_BYTES_PER_ROD_STEP / (mech_ms * 1e-3) * 1e-9 if mech_ms > 0 else None,
+                          "peak": peaks["hbm_gbs"], "unit": "GB/s", "peak_source": peaks_src,
+                          "ms_per_step": mech_ms},
+    }
+    if line["roofline_mech"]["achieved"]:
+        line["roofline_mech"]["frac"] = line["roofline_mech"]["achieved"] / peaks["hbm_gbs"]
+    if world == 1 and not args.no_cpu:
+        cb = cpu_baseline(args.cpu_rods, args.cpu_steps, None)
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -148,6 +148,9 @@ class Library:
                 [u32, C.c_float, P(CrmConfig), u64, P(C.c_float * 2), C.c_float, u32, vp],
             ),
             "sim_launch_count": (u64, [vp]),
+            "sim_step_timed": (C.c_int, [vp, u32, P(C.c_double)]),
+            "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
+            "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),
             "sim_read_timers": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u64)]),
             # oracle only
@@ -235,6 +238,15 @@ class Sim:
 
     def step(self, n_steps: int = 1):
         self.L.check(self.L.fn("sim_step")(self.h, int(n_steps)))
+
+    def step_timed(self, n_steps: int) -> float:
+        """Advance n_steps; returns the device time in ms (CUDA events on the sim's stream)."""
+        ms = C.c_double(0)
+        self.L.check(self.L.fn("sim_step_timed")(self.h, int(n_steps), C.byref(ms)))
+        return float(ms.value)
+
+    def set_exact_math(self, exact: bool):
+        self.L.check(self.L.fn("sim_set_exact_math")(self.h, int(exact)))
 
     def compute_forces(self):
         n, nv = self.n_rods, self.n_vertices

@@ -531,6 +531,24 @@ int crm_sim_step(crm_sim* s, uint32_t n_steps) {
     return 0;
 }
 
+int crm_sim_step_timed(crm_sim* s, uint32_t n_steps, double* ms_out) {
+    CK(cudaSetDevice(s->device));
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    CK(cudaEventRecord(a, s->stream));
+    int rc = 0;
+    for (uint32_t k = 0; k < n_steps && !rc; ++k) rc = step_once(s);
+    CK(cudaEventRecord(b, s->stream));
+    CK(cudaEventSynchronize(b));
+    float ms = 0.0f;
+    CK(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    if (ms_out) *ms_out = ms;
+    return rc;
+}
+
 int crm_sim_run(crm_sim* s) {
     CK(cudaSetDevice(s->device));
     size_t next = 0;

@@ -73,10 +73,10 @@ def _apply(p, kw):
 
 
 def lattice_colony(n_rods: int, domain: float | None = None, n_vertices: int = 8, spring_length: float = 3.0,
-                   spacing=(24.0, 4.0), angle_std: float = 0.1, jitter: float = 0.3, seed: int = 12345,
+                   spacing=(24.0, 4.0), angle_std: float = 0.02, jitter: float = 0.25, seed: int = 12345,
                    z: float = 1.25, z_jitter: float = 0.0, margin: float = 14.0):
     """Jittered nematic lattice (C3): rod centres on a (spacing_x, spacing_y) lattice, angle ~
-    N(0, angle_std), uniform jitter; returns pos[n_rods, n_vertices, 3] f32.  If ``domain`` is
+    N(0, angle_std) clipped at 2.5 sigma, uniform jitter; returns pos[n_rods, n_vertices, 3] f32.  If ``domain`` is
     given the lattice is cut to fit a square domain of that edge (with ``margin``)."""
     rng = np.random.default_rng(seed)
     sx, sy = spacing
@@ -94,7 +94,9 @@ def lattice_colony(n_rods: int, domain: float | None = None, n_vertices: int = 8
     cx = margin + (idx // ny) * sx + rng.uniform(-jitter, jitter, n_rods)
     cy = margin + (idx % ny) * sy + rng.uniform(-jitter, jitter, n_rods)
     cz = z + rng.uniform(-z_jitter, z_jitter, n_rods) if z_jitter else np.full(n_rods, z)
-    ang = rng.normal(0.0, angle_std, n_rods)
+    # clipped so that neighbouring rods (4 um apart) never cross: crossing rods in the z = const
+    # plane put a vertex exactly on a segment in f32 (r = 0 -> NaN, in the reference as well)
+    ang = np.clip(rng.normal(0.0, angle_std, n_rods), -2.5 * angle_std, 2.5 * angle_std)
     t = (np.arange(n_vertices) - (n_vertices - 1) / 2.0) * spring_length
     pos = np.empty((n_rods, n_vertices, 3), dtype=np.float32)
     pos[:, :, 0] = cx[:, None] + t[None, :] * np.cos(ang)[:, None]

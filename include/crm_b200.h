@@ -151,6 +151,10 @@ int crm_sim_run(crm_sim* sim);
 /* Advance `n_steps` mechanics steps without taking snapshots (bench / tests). */
 int crm_sim_step(crm_sim* sim, uint32_t n_steps);
 
+/* Same as crm_sim_step, timed on the device: CUDA events recorded on the sim's own stream
+ * before the first and after the last kernel of the n_steps (ms). */
+int crm_sim_step_timed(crm_sim* sim, uint32_t n_steps, double* ms);
+
 /* Force accumulators the next step would use, i.e. the reference's
  * interaction + domain force for the current state (cellular_raza
  * update_mechanics_interaction_step_1..3 + calculate_custom_domain_force).
@@ -186,6 +190,11 @@ uint64_t crm_sim_rod_steps(const crm_sim* sim);
 int crm_sim_enable_timers(crm_sim* sim, int enable);
 int crm_sim_read_timers(crm_sim* sim, double* force_ms, uint64_t* force_launches,
                         uint64_t* last_pairs_in_cutoff, uint64_t* last_pairs_tested);
+
+/* Non-tensor peaks of the device the force kernel is bounded by (not in the driver's
+ * MEASURED_PEAKS.json): dense FP32 FMA TFLOP/s, MUFU.EX2 Top/s, and the SM clock the FMA
+ * figure implies at 128 lanes/SM/clk. */
+int crm_microbench(int device, double* fp32_tflops, double* mufu_tops, double* sm_mhz_est);
 
 #ifdef __cplusplus
 }

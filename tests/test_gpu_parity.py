@@ -21,7 +21,7 @@ def _pair(cfg, pos, par, product_lib, vel=None, exact=False):
     vel = np.zeros_like(pos) if vel is None else vel
     g = _capi.Sim(product_lib, cfg)
     if exact:
-        product_lib.lib.crm_sim_set_exact_math(g.h, 1)
+        g.set_exact_math(True)
     o = oracle.sim(cfg)
     g.set_agents(pos, vel, par)
     o.set_agents(pos, vel, par)
