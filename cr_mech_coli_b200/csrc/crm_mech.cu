@@ -50,11 +50,8 @@ __global__ void k_bounds(Dev d) {
     if (a >= d.n) return;  // whole groups exit together
     const float* p = d.pos + (size_t)a * 3 * LP;
     float x = p[l], y = p[LP + l], z = p[2 * LP + l];
-    float4 bs = bounding_sphere<NV>(x, y, z, l, m);
-    if (l == 0) {
-        d.bsphere[a] = bs;
-        atomicMax(&d.status->emax_bits, __float_as_uint(bs.w));
-    }
+    const float ext = store_bounds<NV>(d, a, x, y, z, l, m);
+    if (l == 0) atomicMax(&d.status->emax_bits, __float_as_uint(ext));
 }
 
 // ------------------------------------------------------------------------------------
@@ -288,7 +285,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
                 d.status->err_slot = a;
         }
     }
-    float4 bs = bounding_sphere<NV>(Pnew[0], Pnew[1], Pnew[2], l, gm);
+    const float ext = store_bounds<NV>(d, a, Pnew[0], Pnew[1], Pnew[2], l, gm);
     if (dividing) {
         // user voxel of the mother = voxel of the mean vertex at the start of the step,
         // summed sequentially like the reference (nalgebra row_mean)
@@ -317,8 +314,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         gs.z = newL;
         d.grow[a] = gs;
         if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
-        d.bsphere[a] = bs;
-        atomicMax(&d.status->emax_bits, __float_as_uint(bs.w));
+        atomicMax(&d.status->emax_bits, __float_as_uint(ext));
     }
 }
 
@@ -434,8 +430,8 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
             d.force[ob + c * LP + lz] = 0.f;
         }
     }
-    float4 bs1 = bounding_sphere<NV>(D1[0], D1[1], D1[2], l, gm);
-    float4 bs2 = bounding_sphere<NV>(D2[0], D2[1], D2[2], l, gm);
+    const float ext1 = store_bounds<NV>(d, a, D1[0], D1[1], D1[2], l, gm);
+    const float ext2 = store_bounds<NV>(d, b, D2[0], D2[1], D2[2], l, gm);
     if (l == 0) {
         // spring_length *= 1/2 - radius/(n_vertices*spring_length)   (bit-exact op order)
         const float L = gs.z;
@@ -452,9 +448,7 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
         d.cyc[b] = cp;
         d.nn[b] = d.nn[a];
         d.nhist[b] = 0;
-        d.bsphere[a] = bs1;
-        d.bsphere[b] = bs2;
-        atomicMax(&d.status->emax_bits, __float_as_uint(fmaxf(bs1.w, bs2.w)));
+        atomicMax(&d.status->emax_bits, __float_as_uint(fmaxf(ext1, ext2)));
     }
 }
 

@@ -123,6 +123,8 @@ static int reserve(crm_sim* s, uint32_t need) {
     G(s->d.cyc, on, (size_t)cap);
     G(s->d.nn, on, (size_t)cap);
     G(s->d.bsphere, on, (size_t)cap);
+    G(s->d.chord, 2 * on, (size_t)2 * cap);
+    G(s->d.seg, on * 5 * s->lp, (size_t)cap * 5 * s->lp);
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
     G(s->d.sorted, 0, (size_t)cap);
@@ -194,6 +196,7 @@ static void fill_device_params(const crm_rod_params& p, PotParams& pot, MechPara
         pot.b = en;
         pot.c = em;
         pot.d = powf(em / en, 1.0f / (en - em));
+        if (en == std::floor(en) && em == std::floor(em) && em >= 1.0f && en > em && en <= 24.0f) pot.type = CRM_POT_MIE_INT;
     }
     mech = make_float4(p.spring_tension, p.rigidity, p.damping, p.diffusion_constant);
     grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, 0.0f);
@@ -446,7 +449,7 @@ void crm_sim_destroy(crm_sim* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
-                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.cell_of, s->d.cell_rank,
+                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.seg, s->d.cell_of, s->d.cell_rank,
                     s->d.cell_start, s->d.cell_count, s->d.sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
