@@ -196,7 +196,6 @@ static void fill_device_params(const crm_rod_params& p, PotParams& pot, MechPara
         pot.b = en;
         pot.c = em;
         pot.d = powf(em / en, 1.0f / (en - em));
-        if (en == std::floor(en) && em == std::floor(em) && em >= 1.0f && en > em && en <= 24.0f) pot.type = CRM_POT_MIE_INT;
     }
     mech = make_float4(p.spring_tension, p.rigidity, p.damping, p.diffusion_constant);
     grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, 0.0f);
