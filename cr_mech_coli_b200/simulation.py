@@ -1,0 +1,90 @@
+"""Entry points of the drop-in boundary (reference src/simulation.rs): ``generate_positions``,
+``generate_agents``, ``run_simulation_with_agents``, ``sort_cellular_identifiers``.  All compute goes
+through the C ABI of ``libcrm_b200.so``; there is no CPU fallback."""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from .cell_container import CellContainer, _Snapshot
+from .datatypes import AgentSettings, Configuration, PhysicalInteraction, RodAgent, StorageOption
+
+SimulationError = _capi.SimulationError
+
+
+def generate_positions(n_agents, agent_settings: AgentSettings, config: Configuration, rng_seed=0, dx=(0.0, 0.0),
+                       randomize_positions=0.0, n_vertices=8):
+    """reference src/simulation.rs:17-51 -> ``_generate_positions`` (:107-166), ChaCha8-stream exact."""
+    lib = _capi.product()
+    out = np.zeros((int(n_agents), int(n_vertices), 3), dtype=np.float32)
+    cfg = config._to_c()
+    dxa = (C.c_float * 2)(float(dx[0]), float(dx[1]))
+    rc = lib.fn("generate_positions")(int(n_agents), float(agent_settings.mechanics.spring_length), C.byref(cfg),
+                                      int(rng_seed), C.byref(dxa), float(randomize_positions), int(n_vertices),
+                                      out.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        # rand panics on an empty sampling range (rods do not fit into their chunk)
+        raise ValueError("cannot sample empty range: the domain is too small for the requested agents")
+    return [out[k].copy() for k in range(int(n_agents))]
+
+
+def generate_agents(n_agents, agent_settings: AgentSettings, config: Configuration, rng_seed=0, dx=(0.0, 0.0),
+                    randomize_positions=0.0, n_vertices=8):
+    """reference src/simulation.rs:56-104"""
+    positions = generate_positions(n_agents, agent_settings, config, rng_seed, dx, randomize_positions, n_vertices)
+    m = agent_settings.mechanics
+    vel0 = m.vel
+    agents = []
+    for pos in positions:
+        vel = vel0 if vel0.shape == pos.shape else np.zeros_like(pos)
+        agents.append(RodAgent(
+            pos, vel, PhysicalInteraction(agent_settings.interaction), m.diffusion_constant, m.spring_tension,
+            m.rigidity, m.spring_length, m.damping, agent_settings.growth_rate, agent_settings.growth_rate_setter,
+            agent_settings.spring_length_threshold, agent_settings.spring_length_threshold_setter,
+            agent_settings.neighbor_reduction))
+    return agents
+
+
+def pack_agents(agents):
+    """list[RodAgent] -> (pos, vel, params) arrays of the C ABI."""
+    n = len(agents)
+    nv = agents[0]._pos.shape[0] if n else 8
+    pos = np.zeros((n, nv, 3), np.float32)
+    vel = np.zeros((n, nv, 3), np.float32)
+    par = np.zeros(n, _capi.ROD_PARAMS_DTYPE)
+    for k, a in enumerate(agents):
+        if a._pos.shape[0] != nv:
+            raise ValueError("all agents must have the same number of vertices")
+        pos[k], vel[k] = a._pos, a._vel
+        a._to_record(par[k])
+    return pos, vel, par
+
+
+def run_simulation_with_agents(config: Configuration, agents, device: int = 0) -> CellContainer:
+    """reference src/simulation.rs:232-319.  Agents are copied in, the whole run executes on the GPU
+    (``crm_sim_run``), snapshots come back at the save points as packed arrays."""
+    unsupported = [o for o in config.storage_options if o != StorageOption.Memory]
+    if unsupported:
+        raise NotImplementedError(f"storage options {unsupported} are not implemented (Memory only)")
+    agents = list(agents)
+    lib = _capi.product()
+    pos, vel, par = pack_agents(agents)
+    with _capi.Sim(lib, config._to_c(), device) as sim:
+        if len(agents):
+            sim.set_agents(pos, vel, par)
+            sim.run()
+            snaps = [_Snapshot(*s) for s in sim.snapshots()]
+        else:
+            its, _ = lib.save_schedule(sim.cfg)
+            e = np.zeros((0, 8, 3), np.float32)
+            snaps = [_Snapshot(int(i), e, e, np.zeros(0, _capi.ROD_PARAMS_DTYPE), np.zeros(0, _capi.IDENT_DTYPE),
+                               np.zeros(0, _capi.IDENT_DTYPE)) for i in its]
+    return CellContainer(path=None, _snapshots=snaps)
+
+
+def sort_cellular_identifiers(identifiers):
+    """reference src/simulation.rs:332-339"""
+    return sorted(identifiers)

@@ -23,6 +23,25 @@ from __future__ import annotations
 
 import numpy as np
 
+import ctypes
+import ctypes.util
+
+# Rust's f32::cos / f32::sin call the platform libm (glibc cosf/sinf on the reference's Linux targets);
+# numpy's SIMD float32 kernels differ from it by an ulp on some arguments.
+_libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+for _f in (_libm.cosf, _libm.sinf):
+    _f.restype = ctypes.c_float
+    _f.argtypes = [ctypes.c_float]
+
+
+def _cosf(x):
+    return np.float32(_libm.cosf(float(x)))
+
+
+def _sinf(x):
+    return np.float32(_libm.sinf(float(x)))
+
+
 M32 = 0xFFFFFFFF
 M64 = 0xFFFFFFFFFFFFFFFF
 f32 = np.float32
@@ -130,17 +149,17 @@ def generate_positions(n_agents, spring_length, domain_size, domain_height, rng_
             rng.range_f32(f32(0.4) * H, f32(0.6) * H),
         ]
         angle = rng.range_f32(f32(0.0), f32(f32(2.0) * f32(np.pi)))
-        p1 = [f32(mid[0] - f32(half * np.cos(angle, dtype=np.float32))),
-              f32(mid[1] - f32(half * np.sin(angle, dtype=np.float32))),
+        p1 = [f32(mid[0] - f32(half * _cosf(angle))),
+              f32(mid[1] - f32(half * _sinf(angle))),
               f32(mid[2] - f32(half * f32(0.0)))]
         pos = np.zeros((n_vertices, 3), dtype=np.float32)
         for c in range(3):  # nalgebra from_fn is column-major
             for r in range(n_vertices):
                 a = f32(f32(f32(r) * spring_length) * s_gen())
                 if c == 0:
-                    b = np.cos(f32(angle * s_gen()), dtype=np.float32)
+                    b = _cosf(f32(angle * s_gen()))
                 elif c == 1:
-                    b = np.sin(f32(angle * s_gen()), dtype=np.float32)
+                    b = _sinf(f32(angle * s_gen()))
                 else:
                     b = f32(0.0)
                 pos[r, c] = f32(p1[c] + f32(a * b))

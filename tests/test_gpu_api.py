@@ -1,0 +1,63 @@
+"""The public Python API on the GPU: README example (reference README.md:24-38, tests/test_getting_started.py)
+and the colour assignment after a simulation (reference tests/test_counter_color_conversion.py:23-49)."""
+import numpy as np
+import pytest
+
+import cr_mech_coli_b200 as crm
+from cr_mech_coli_b200 import _capi
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def test_getting_started(product_lib):
+    config = crm.Configuration()
+    agents = crm.generate_agents(4, crm.AgentSettings(), config)
+    cc = crm.run_simulation_with_agents(config, agents)
+    its = cc.get_all_iterations()
+    assert its == [0, 91, 182, 273, 364, 455, 545, 636, 727, 818, 909, 1000]  # n_saves + 2 snapshots
+    first, last = cc.get_cells_at_iteration(0), cc.get_cells_at_iteration(1000)
+    assert len(first) == 4 and len(last) == 8  # every rod divided once (growth 0.01, threshold 6)
+    I = crm.CellIdentifier.new_initial
+    assert sorted(first) == [I(k) for k in range(4)]
+    assert all(np.array_equal(first[I(k)][0].pos, agents[k].pos) for k in range(4))
+    dm = cc.get_daughter_map()
+    assert sorted(dm) == [I(k) for k in range(4)] and all(len(v) == 2 for v in dm.values())
+    assert all(cc.get_parent(d) == p for p, ds in dm.items() for d in ds)
+    # the same run through the oracle gives the same lineage
+    pos = np.stack([a.pos for a in agents])
+    from cr_mech_coli_b200.simulation import pack_agents
+    with oracle.sim(config._to_c()) as o:
+        o.set_agents(*pack_agents(agents))
+        o.run()
+        ids = o.snapshots()[-1][4]
+    assert sorted(last) == sorted(crm.CellIdentifier._from_record(r) for r in ids)
+
+
+def test_assign_colors_after_simulation(product_lib):
+    config = crm.Configuration(t_max=20.0)
+    s = crm.AgentSettings()
+    positions = crm.generate_positions(8, s, config)
+    agents = [crm.RodAgent(pos=p, vel=p * 0.0, **s.to_rod_agent_dict()) for p in positions]
+    cc = crm.run_simulation_with_agents(config, agents)
+    cells = cc.get_cells()[cc.get_all_iterations()[0]]
+    for n, ident in enumerate(sorted(cells)):
+        assert cc.cell_to_color[ident] == crm.counter_to_color(n + 1)
+        assert cc.get_cell_from_color(cc.cell_to_color[ident]) == ident
+
+
+def test_simulation_error_is_raised(product_lib):
+    config = crm.Configuration(domain_size=(60.0, 60.0), t_max=5.0)
+    s = crm.AgentSettings()
+    p = np.zeros((8, 3), np.float32)
+    p[:, 0] = 10 + 3 * np.arange(8)
+    p[:, 1:] = (30.0, 1.25)
+    v = np.zeros_like(p)
+    v[:, 1] = 5e3
+    with pytest.raises(crm.SimulationError, match="BoundaryError"):
+        crm.run_simulation_with_agents(config, [crm.RodAgent(pos=p, vel=v, **s.to_rod_agent_dict())])
+
+
+def test_empty_agent_list(product_lib):
+    cc = crm.run_simulation_with_agents(crm.Configuration(t_max=1.0, n_saves=1), [])
+    assert cc.get_all_iterations() == [0, 5, 10] and cc.get_cells_at_iteration(5) == {}
