@@ -132,6 +132,12 @@ __global__ void k_bin_sort(Dev d, uint32_t ncells) {
         }
         d.sorted[j] = v;
     }
+    for (uint32_t i = s; i < e; ++i) {  // cell-sorted copies of the bounds for the force kernel's candidate scan
+        const uint32_t v = d.sorted[i];
+        d.bs_sorted[i] = d.bsphere[v];
+        d.chord_sorted[2 * i] = d.chord[2 * v];
+        d.chord_sorted[2 * i + 1] = d.chord[2 * v + 1];
+    }
 }
 
 

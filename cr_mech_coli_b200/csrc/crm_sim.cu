@@ -124,10 +124,12 @@ static int reserve(crm_sim* s, uint32_t need) {
     G(s->d.nn, on, (size_t)cap);
     G(s->d.bsphere, on, (size_t)cap);
     G(s->d.chord, 2 * on, (size_t)2 * cap);
-    G(s->d.seg, on * 5 * s->lp, (size_t)cap * 5 * s->lp);
+    G(s->d.vrec, on * s->lp, (size_t)cap * s->lp);
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
     G(s->d.sorted, 0, (size_t)cap);
+    G(s->d.bs_sorted, 0, (size_t)cap);
+    G(s->d.chord_sorted, 0, (size_t)2 * cap);
     G(s->d.divlist, 0, (size_t)cap);
     G(s->stage, 0, (size_t)cap * s->nv * 3);
 #undef G
@@ -448,8 +450,8 @@ void crm_sim_destroy(crm_sim* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
-                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.seg, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->d.sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.cell_of, s->d.cell_rank,
+                    s->d.cell_start, s->d.cell_count, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -498,6 +500,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         cmax = std::max(cmax, par[a].cutoff);
     }
     s->rsearch = std::max(cmax, 2.0f * rmax * 0.70710678f) * 1.0001f;
+    s->d.rsearch = s->rsearch;  // the bounds kernels bake it into the cull thresholds
     const size_t m = (size_t)n * nv * 3;
     if (n) {
         CK(cudaMemcpyAsync(s->stage, pos, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
