@@ -153,6 +153,23 @@ class Library:
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),
             "sim_read_timers": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u64)]),
+            # sharding (product only)
+            "sim_set_slab": (C.c_int, [vp, C.c_float, C.c_float]),
+            "sim_set_global_slots": (C.c_int, [vp, vp, u32]),
+            "sim_get_global_slots": (C.c_int, [vp, vp]),
+            "sim_halo_record_bytes": (u32, [vp]),
+            "sim_migrant_record_bytes": (u32, [vp]),
+            "sim_max_extent": (C.c_float, [vp]),
+            "sim_search_radius": (C.c_float, [vp]),
+            "sim_halo_pack": (C.c_int, [vp, C.c_int, C.c_float, vp, u32, P(u32)]),
+            "sim_set_ghosts": (C.c_int, [vp, vp, u32, vp, u32, C.c_float]),
+            "sim_migrate_out": (C.c_int, [vp, vp, u32, P(u32), vp, u32, P(u32)]),
+            "sim_migrate_in": (C.c_int, [vp, vp, u32]),
+            "sim_n_leaving": (u32, [vp]),
+            "sim_pending_divisions": (u32, [vp, vp, vp, u32]),
+            "sim_apply_divisions": (C.c_int, [vp, vp, vp, vp, u32]),
+            "sim_take_snapshot": (C.c_int, [vp]),
+            "sim_snapshot_global_slots": (C.c_int, [vp, u32, vp]),
             # oracle only
             "sim_pairs_in_cutoff": (u64, [vp]),
             "num_threads": (C.c_int, []),
@@ -314,7 +331,7 @@ def product() -> Library:
     global _PRODUCT
     if _PRODUCT is None:
         _PRODUCT = Library(_PKG_DIR / LIB_NAME, "crm_")
-        if _PRODUCT.fn("abi_version")() != 1:
+        if _PRODUCT.fn("abi_version")() != 2:
             raise ImportError("libcrm_b200.so: ABI version mismatch")
     return _PRODUCT
 

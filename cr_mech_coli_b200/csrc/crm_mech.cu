@@ -47,7 +47,7 @@ __global__ void k_bounds(Dev d) {
     uint32_t a = tid / LP;
     int l = threadIdx.x % LP;
     unsigned m = group_mask<LP>();
-    if (a >= d.n) return;  // whole groups exit together
+    if (a >= d.n_own) return;  // whole groups exit together
     const float* p = d.pos + (size_t)a * 3 * LP;
     float x = p[l], y = p[LP + l], z = p[2 * LP + l];
     const float ext = store_bounds<NV>(d, a, x, y, z, l, m);
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const uint32_t a = tid / LP;
     const int l = threadIdx.x % LP;
     const unsigned gm = group_mask<LP>();
-    if (a >= d.n) return;
+    if (a >= d.n_own) return;
     const size_t o = (size_t)a * STRIDE;
     const bool hv = l < NV;
     const int li = hv ? l : 0;
@@ -291,7 +291,9 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
                 d.status->err_slot = a;
         }
     }
-    const float ext = store_bounds<NV>(d, a, Pnew[0], Pnew[1], Pnew[2], l, gm);
+    float cx;
+    const float ext = store_bounds<NV>(d, a, Pnew[0], Pnew[1], Pnew[2], l, gm, &cx);
+    if (l == 0 && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);
     if (dividing) {
         // user voxel of the mother = voxel of the mean vertex at the start of the step,
         // summed sequentially like the reference (nalgebra row_mean)
@@ -478,8 +480,8 @@ void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t 
 #undef X
 }
 void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st) {
-    if (d.n == 0) return;
-#define X(NVV) if (nv == NVV) k_bounds<NVV><<<blocks_for((uint64_t)d.n * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
+    if (d.n_own == 0) return;
+#define X(NVV) if (nv == NVV) k_bounds<NVV><<<blocks_for((uint64_t)d.n_own * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
     CRM_NV_LIST(X)
 #undef X
 }
@@ -494,8 +496,8 @@ int launch_binning(const Dev& d, cudaStream_t st) {
     return 4;
 }
 void launch_integrate(int nv, const Dev& d, cudaStream_t st) {
-    if (d.n == 0) return;
-#define X(NVV) if (nv == NVV) k_integrate<NVV><<<blocks_for((uint64_t)d.n * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
+    if (d.n_own == 0) return;
+#define X(NVV) if (nv == NVV) k_integrate<NVV><<<blocks_for((uint64_t)d.n_own * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
     CRM_NV_LIST(X)
 #undef X
 }

@@ -2,37 +2,13 @@
 // include/crm_b200.h.  Replaces the run_main! driver of the reference
 // (src/simulation.rs:234-319): save schedule, per-step kernel sequence, division
 // bookkeeping (CellIdentifier / parent assignment), snapshots.
-#include <algorithm>
-#include <cmath>
-#include <cstdarg>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
-
-#include "crm_device.cuh"
-
-namespace crm {
-// launchers (crm_kernels.cu)
-bool nv_supported(int nv);
-int lanes_per_rod(int nv);
-void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
-void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
-void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
-int launch_binning(const Dev& d, cudaStream_t st);
-void launch_force(int nv, const Dev& d, bool fast, bool count, cudaStream_t st);
-void launch_integrate(int nv, const Dev& d, cudaStream_t st);
-void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st);
-// host helpers (crm_host.cpp)
-int build_save_schedule(const crm_config* c, std::vector<uint64_t>& out, uint64_t& max_iter, std::string& err);
-}  // namespace crm
+#include "crm_sim.h"
 
 using namespace crm;
 
 static thread_local std::string g_err;
 
-static int fail(int code, const char* fmt, ...) {
+int crm_fail(int code, const char* fmt, ...) {
     char buf[1024];
     va_list ap;
     va_start(ap, fmt);
@@ -41,52 +17,7 @@ static int fail(int code, const char* fmt, ...) {
     g_err = buf;
     return code;
 }
-
-#define CK(call)                                                                               \
-    do {                                                                                       \
-        cudaError_t e_ = (call);                                                               \
-        if (e_ != cudaSuccess)                                                                 \
-            return fail(CRM_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),  \
-                        __FILE__, __LINE__);                                                   \
-    } while (0)
-
-struct HostSnap {
-    uint64_t iteration;
-    uint32_t n;
-    std::vector<float> pos, vel;
-    std::vector<crm_rod_params> par;
-    std::vector<crm_ident> ids, parents;
-};
-
-struct crm_sim {
-    crm_config cfg{};
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    int nv = 0, lp = 0;
-    uint32_t n = 0, cap = 0;
-    uint32_t ncells_cap = 0;
-    Dev d{};
-    float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
-    Status* h_status = nullptr;  // pinned
-    float emax = 0.0f;
-    float rsearch = 0.0f;
-    bool fast_math = true;
-    // host-side bookkeeping
-    std::vector<crm_rod_params> base;  // cold fields per slot
-    std::vector<crm_ident> ids, parents;
-    std::vector<uint64_t> vox_counter;
-    std::vector<DivRecord> h_div;
-    uint64_t iteration = 0, rod_steps = 0, launches = 0;
-    std::vector<uint64_t> save_iter;
-    uint64_t max_iter = 0;
-    std::vector<HostSnap> snaps;
-    // timers
-    bool timers = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    double force_ms = 0.0;
-    uint64_t force_launches = 0;
-    uint64_t last_pairs_cut = 0, last_pairs_tested = 0;
-};
+#define fail crm_fail
 
 template <class T>
 static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st) {
@@ -101,7 +32,7 @@ static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st) 
 }
 
 // grow every per-rod array to `need` slots, preserving the first s->n
-static int reserve(crm_sim* s, uint32_t need) {
+int crm_reserve(crm_sim* s, uint32_t need) {
     if (need <= s->cap) return 0;
     uint32_t cap = s->cap ? s->cap : 1024;
     while (cap < need) cap *= 2;
@@ -153,7 +84,7 @@ static int reserve_cells(crm_sim* s, uint32_t ncells) {
 // Centroid cell list geometry: the 3x3 stencil is complete when the cell edge is at
 // least 2*max_extent + search radius.
 static int configure_grid(crm_sim* s) {
-    const float h = (2.0f * s->emax + s->rsearch) * 1.0005f + 1e-4f;
+    const float h = (2.0f * std::max(s->emax, s->n_ghost ? s->emax_ghost : 0.0f) + s->rsearch) * 1.0005f + 1e-4f;
     double ncx = std::floor((double)s->cfg.domain_size[0] / h), ncy = std::floor((double)s->cfg.domain_size[1] / h);
     if (!(ncx >= 1.0)) ncx = 1.0;
     if (!(ncy >= 1.0)) ncy = 1.0;
@@ -180,7 +111,7 @@ static float cutoff_threshold(float c) {
     return x;
 }
 
-static void fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams& mech, GrowState& grow,
+void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams& mech, GrowState& grow,
                                CycleParams& cyc) {
     pot.type = p.potential;
     pot.radius = p.radius;
@@ -213,13 +144,13 @@ static void fill_device_params(const crm_rod_params& p, PotParams& pot, MechPara
     cyc.nr_exp = p.neighbor_reduction_exp;
 }
 
-static int read_status(crm_sim* s) {
+int crm_read_status(crm_sim* s) {
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     return 0;
 }
 
-static int report_device_error(crm_sim* s) {
+int crm_report_device_error(crm_sim* s) {
     const Status& st = *s->h_status;
     if (st.err_code == 0) return 0;
     std::vector<float> rod((size_t)3 * s->lp);
@@ -239,56 +170,84 @@ static int report_device_error(crm_sim* s) {
                 st.err_slot, (unsigned long long)s->iteration);
 }
 
-// Divisions of this step: order the mothers by slot, run the geometry kernel, then do the
-// identifier bookkeeping of the backend's update_cell_cycle_4 on the host (mothers are renamed
-// first, then the new cells, with the per-voxel pre-incremented counter).
-static int handle_divisions(crm_sim* s, uint32_t n_div) {
-    const uint32_t n0 = s->n;
+// Divisions of this step.  fetch_divisions orders the mothers by global slot (= slot when the run
+// is not sharded); apply_divisions runs the geometry kernel and installs the identifiers of the
+// backend's update_cell_cycle_4 (mothers are renamed first, then the new cells, with the per-voxel
+// pre-incremented counter).  Unsharded runs derive the identifiers here; sharded runs get them from
+// the coordinator, which sees the divisions of all slabs (crm_sim_apply_divisions).
+static int fetch_divisions(crm_sim* s, uint32_t n_div) {
     s->h_div.resize(n_div);
     CK(cudaMemcpyAsync(s->h_div.data(), s->d.divlist, sizeof(DivRecord) * n_div, cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
-    std::sort(s->h_div.begin(), s->h_div.end(), [](const DivRecord& a, const DivRecord& b) { return a.slot < b.slot; });
+    std::sort(s->h_div.begin(), s->h_div.end(),
+              [s](const DivRecord& a, const DivRecord& b) { return s->gslot[a.slot] < s->gslot[b.slot]; });
     for (uint32_t r = 0; r < n_div; ++r) {
         const crm_rod_params& p = s->base[s->h_div[r].slot];
         if (!(p.radius > 0.0f))
             return fail(CRM_ERR_DIVISION, "DivisionError: cannot divide rod slot %u (radius %g)", s->h_div[r].slot, p.radius);
     }
-    int rc = reserve(s, n0 + n_div);
+    return 0;
+}
+
+int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident* id_daughter,
+                           const uint64_t* gslot_daughter) {
+    const uint32_t n0 = s->n, n_div = (uint32_t)s->h_div.size();
+    int rc = crm_reserve(s, n0 + n_div);
     if (rc) return rc;
     CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
-    s->d.n = n0;
     launch_divide(s->nv, s->d, n_div, n0, s->stream);
     s->launches += 1;
     CK(cudaGetLastError());
-    if ((rc = read_status(s))) return rc;
-    if ((rc = report_device_error(s))) return rc;
-    // identifiers
-    const uint32_t nvox = s->cfg.n_voxels[0] * s->cfg.n_voxels[1];
-    std::vector<uint32_t> per_vox(nvox, 0), rank_vox(nvox, 0);
-    for (uint32_t r = 0; r < n_div; ++r) per_vox[s->h_div[r].uvox]++;
+    if ((rc = crm_read_status(s))) return rc;
+    if ((rc = crm_report_device_error(s))) return rc;
     s->base.resize(n0 + n_div);
     s->ids.resize(n0 + n_div);
     s->parents.resize(n0 + n_div);
+    s->gslot.resize(n0 + n_div);
     for (uint32_t r = 0; r < n_div; ++r) {
-        const uint32_t a = s->h_div[r].slot, b = n0 + r, v = s->h_div[r].uvox;
+        const uint32_t a = s->h_div[r].slot, b = n0 + r;
         const crm_ident mother = s->ids[a];
-        const uint32_t k = rank_vox[v]++;
-        s->ids[a] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + 1 + k};
+        s->ids[a] = id_mother[r];
         s->parents[a] = mother;
-        s->ids[b] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + per_vox[v] + 1 + k};
+        s->ids[b] = id_daughter[r];
         s->parents[b] = mother;
         s->base[b] = s->base[a];
+        s->gslot[b] = gslot_daughter[r];
+    }
+    s->n = n0 + n_div;
+    s->n_ghost = 0;  // the new cells took the first ghost slots; ghosts are re-sent every step
+    s->d.n = s->d.n_own = s->n;
+    s->emax = std::max(s->emax, __builtin_bit_cast(float, s->h_status->emax_bits));
+    s->h_div.clear();
+    s->pending_div = 0;
+    return 0;
+}
+
+static int handle_divisions(crm_sim* s, uint32_t n_div) {
+    int rc = fetch_divisions(s, n_div);
+    if (rc) return rc;
+    const uint32_t n0 = s->n;
+    const uint32_t nvox = s->cfg.n_voxels[0] * s->cfg.n_voxels[1];
+    std::vector<uint32_t> per_vox(nvox, 0), rank_vox(nvox, 0);
+    for (uint32_t r = 0; r < n_div; ++r) per_vox[s->h_div[r].uvox]++;
+    std::vector<crm_ident> idm(n_div), idd(n_div);
+    std::vector<uint64_t> gs(n_div);
+    for (uint32_t r = 0; r < n_div; ++r) {
+        const uint32_t v = s->h_div[r].uvox;
+        const uint32_t k = rank_vox[v]++;
+        idm[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + 1 + k};
+        idd[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + per_vox[v] + 1 + k};
+        gs[r] = (uint64_t)n0 + r;
     }
     for (uint32_t v = 0; v < nvox; ++v) s->vox_counter[v] += 2ull * per_vox[v];
-    s->n = n0 + n_div;
-    s->d.n = s->n;
-    return 0;
+    return crm_apply_divisions(s, idm.data(), idd.data(), gs.data());
 }
 
 static int launch_neighbour_and_force(crm_sim* s, bool count) {
     int rc = configure_grid(s);
     if (rc) return rc;
-    s->d.n = s->n;
+    s->d.n = s->n + s->n_ghost;
+    s->d.n_own = s->n;
     s->d.rsearch = s->rsearch;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     s->launches += launch_binning(s->d, s->stream);
@@ -300,6 +259,7 @@ static int launch_neighbour_and_force(crm_sim* s, bool count) {
 }
 
 static int step_once(crm_sim* s) {
+    if (s->pending_div) return fail(CRM_ERR_INVALID, "divisions of the last step are pending (crm_sim_apply_divisions)");
     if (s->n == 0) {
         s->iteration += 1;
         return 0;
@@ -312,19 +272,23 @@ static int step_once(crm_sim* s) {
     launch_integrate(s->nv, s->d, s->stream);
     s->launches += 1;
     CK(cudaGetLastError());
-    if ((rc = read_status(s))) return rc;
+    if ((rc = crm_read_status(s))) return rc;
     if (s->timers) {
         float ms = 0.0f;
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         s->force_ms += ms;
         s->force_launches += 1;
     }
-    if ((rc = report_device_error(s))) return rc;
-    s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    if ((rc = crm_report_device_error(s))) return rc;
+    s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);  // owned rods; ghosts are re-sent before the next step
     const uint32_t n_div = s->h_status->n_div;
     if (n_div) {
-        if ((rc = handle_divisions(s, n_div))) return rc;
-        s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+        if (s->sharded) {  // identifiers need the divisions of all slabs: crm_sim_apply_divisions
+            if ((rc = fetch_divisions(s, n_div))) return rc;
+            s->pending_div = n_div;
+        } else if ((rc = handle_divisions(s, n_div))) {
+            return rc;
+        }
     }
     return 0;
 }
@@ -359,7 +323,7 @@ static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* pa
     return 0;
 }
 
-static int take_snapshot(crm_sim* s) {
+int crm_take_snapshot(crm_sim* s) {
     s->snaps.emplace_back();
     HostSnap& sn = s->snaps.back();
     sn.iteration = s->iteration;
@@ -370,6 +334,7 @@ static int take_snapshot(crm_sim* s) {
     sn.par.resize(s->n);
     sn.ids.assign(s->ids.begin(), s->ids.begin() + s->n);
     sn.parents.assign(s->parents.begin(), s->parents.begin() + s->n);
+    sn.gslot.assign(s->gslot.begin(), s->gslot.begin() + s->n);
     return download_state(s, sn.pos.data(), sn.vel.data(), sn.par.data());
 }
 
@@ -441,6 +406,8 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     s->d.surface_friction = c->surface_friction;
     s->d.surface_friction_distance = c->surface_friction_distance;
     s->d.dt = c->dt;
+    s->d.slab_lo = -INFINITY;
+    s->d.slab_hi = INFINITY;
     s->d.seed = c->rng_seed;
     *out = s;
     return 0;
@@ -451,7 +418,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -475,7 +442,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->nv = (int)nv;
     s->lp = lanes_per_rod((int)nv);
     s->n = 0;
-    int rc = reserve(s, std::max<uint32_t>(n + n / 2 + 16, 1024));
+    int rc = crm_reserve(s, std::max<uint32_t>(n + n / 2 + 16, 1024));
     if (rc) return rc;
     s->iteration = 0;
     s->snaps.clear();
@@ -483,6 +450,9 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->base.assign(par, par + n);
     s->ids.resize(n);
     s->parents.resize(n);
+    s->gslot.resize(n);
+    s->n_ghost = 0;
+    s->pending_div = 0;
     std::vector<PotParams> pot(n);
     std::vector<MechParams> mech(n);
     std::vector<GrowState> grow(n);
@@ -491,10 +461,11 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     float rmax = 0.0f, cmax = 0.0f;
     for (uint32_t a = 0; a < n; ++a) {
         s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, a};
+        s->gslot[a] = a;
         s->parents[a] = crm_ident{-1, 0, 0};
         if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE)
             return fail(CRM_ERR_INVALID, "rod %u: unknown potential %d", a, par[a].potential);
-        fill_device_params(par[a], pot[a], mech[a], grow[a], cyc[a]);
+        crm_fill_device_params(par[a], pot[a], mech[a], grow[a], cyc[a]);
         nn[a] = par[a].n_neighbors;
         rmax = std::max(rmax, par[a].radius);
         cmax = std::max(cmax, par[a].cutoff);
@@ -516,11 +487,11 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         CK(cudaMemsetAsync(s->d.nhist, 0, n, s->stream));
         CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
         s->n = n;
-        s->d.n = n;
+        s->d.n = s->d.n_own = n;
         launch_bounds_kernel(s->nv, s->d, s->stream);
         s->launches += 3;
         CK(cudaGetLastError());
-        if ((rc = read_status(s))) return rc;
+        if ((rc = crm_read_status(s))) return rc;
         s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
         if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite initial positions");
     }
@@ -560,14 +531,14 @@ int crm_sim_run(crm_sim* s) {
     int rc;
     while (next < s->save_iter.size() && s->save_iter[next] < s->iteration) next++;
     if (next < s->save_iter.size() && s->save_iter[next] == s->iteration) {
-        if ((rc = take_snapshot(s))) return rc;
+        if ((rc = crm_take_snapshot(s))) return rc;
         next++;
     }
     while (s->iteration < s->max_iter) {
         if ((rc = step_once(s))) return rc;
         while (next < s->save_iter.size() && s->save_iter[next] < s->iteration) next++;
         if (next < s->save_iter.size() && s->save_iter[next] == s->iteration) {
-            if ((rc = take_snapshot(s))) return rc;
+            if ((rc = crm_take_snapshot(s))) return rc;
             next++;
         }
     }
@@ -580,7 +551,7 @@ int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
     int rc = launch_neighbour_and_force(s, true);
     if (rc) return rc;
     CK(cudaGetLastError());
-    if ((rc = read_status(s))) return rc;
+    if ((rc = crm_read_status(s))) return rc;
     s->last_pairs_cut = s->h_status->pairs_in_cutoff;
     s->last_pairs_tested = s->h_status->pairs_tested;
     if (out_force) {

@@ -1,0 +1,99 @@
+// crm_sim.h — private definition of the simulation object shared by the host translation units
+// (crm_sim.cu: stepping + C ABI; crm_shard.cu: voxel-slab sharding).  Not part of the C ABI.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "crm_device.cuh"
+
+namespace crm {
+// launchers (crm_mech.cu / crm_force.cu)
+bool nv_supported(int nv);
+int lanes_per_rod(int nv);
+void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
+void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
+void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
+int launch_binning(const Dev& d, cudaStream_t st);
+void launch_force(int nv, const Dev& d, bool fast, bool count, cudaStream_t st);
+void launch_integrate(int nv, const Dev& d, cudaStream_t st);
+void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st);
+// host helpers (crm_host.cpp)
+int build_save_schedule(const crm_config* c, std::vector<uint64_t>& out, uint64_t& max_iter, std::string& err);
+}  // namespace crm
+
+// records `fmt...` as the calling thread's last error and returns `code`
+int crm_fail(int code, const char* fmt, ...);
+
+#define CK(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return crm_fail(CRM_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                            __FILE__, __LINE__);                                                  \
+    } while (0)
+
+struct HostSnap {
+    uint64_t iteration;
+    uint32_t n;
+    std::vector<float> pos, vel;
+    std::vector<crm_rod_params> par;
+    std::vector<crm_ident> ids, parents;
+    std::vector<uint64_t> gslot;
+};
+
+struct crm_sim {
+    crm_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int nv = 0, lp = 0;
+    uint32_t n = 0, cap = 0;  // owned rods, slot capacity (owned + ghosts)
+    uint32_t n_ghost = 0;     // ghost rods in slots [n, n + n_ghost)
+    uint32_t ncells_cap = 0;
+    crm::Dev d{};
+    float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
+    crm::Status* h_status = nullptr;  // pinned
+    float emax = 0.0f;        // max centroid->vertex extent over owned rods
+    float emax_ghost = 0.0f;  // ... over the current ghost rods
+    float rsearch = 0.0f;
+    bool fast_math = true;
+    // host-side bookkeeping
+    std::vector<crm_rod_params> base;  // cold fields per slot
+    std::vector<crm_ident> ids, parents;
+    std::vector<uint64_t> gslot;       // global slot (= slot of the unsharded run) per owned slot
+    std::vector<uint64_t> vox_counter;
+    std::vector<crm::DivRecord> h_div;
+    uint64_t iteration = 0, rod_steps = 0, launches = 0;
+    std::vector<uint64_t> save_iter;
+    uint64_t max_iter = 0;
+    std::vector<HostSnap> snaps;
+    // sharding (crm_shard.cu)
+    bool sharded = false;      // divisions are deferred to crm_sim_apply_divisions
+    float slab_lo = -INFINITY, slab_hi = INFINITY;
+    uint32_t pending_div = 0;  // divisions of the last step awaiting crm_sim_apply_divisions
+    void* select_tmp = nullptr;  // cub temp storage
+    size_t select_tmp_bytes = 0;
+    uint32_t* select_out = nullptr;  // [select_cap] selected slots
+    uint32_t select_cap = 0;
+    uint32_t* select_count = nullptr;
+    // timers
+    bool timers = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double force_ms = 0.0;
+    uint64_t force_launches = 0;
+    uint64_t last_pairs_cut = 0, last_pairs_tested = 0;
+};
+
+// shared host helpers (crm_sim.cu)
+int crm_take_snapshot(crm_sim* s);
+int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident* id_daughter, const uint64_t* gslot_daughter);
+void crm_fill_device_params(const crm_rod_params& p, crm::PotParams& pot, crm::MechParams& mech, crm::GrowState& grow,
+                            crm::CycleParams& cyc);
+int crm_reserve(crm_sim* s, uint32_t need);
+int crm_read_status(crm_sim* s);
+int crm_report_device_error(crm_sim* s);

@@ -1,0 +1,520 @@
+"""Voxel-slab sharding of one colony over several GPUs.
+
+The reference splits its voxel grid into ``Configuration.n_threads`` sub-domains that exchange
+boundary-voxel agents and returned forces every step (reference src/simulation.rs:251-256,283-292).
+Here every GPU owns the rods whose centroid x lies in its slab ``[lo, hi)``:
+
+    per step   pack halo records -> send/recv to the two slab neighbours (NCCL over NVLink)
+               -> ghosts -> binning + force + integrate on the owned rods
+               -> all_gather {divisions, leavers} -> division identifiers / migration if any
+
+Forces are gathered by the owner, so no force travels back (one exchange instead of the
+reference's two).  Identifiers, division order and snapshots are keyed by the *global slot* (the
+slot a rod has in the unsharded run), which makes lineage independent of the partition.
+
+Host-side logic (``SlabPartition``, ``assign_division_ids``, ``merge_snapshots``) is plain numpy and
+is exercised on CPU with ``gloo`` (tests/test_sharded_host.py); device work goes through the C ABI
+(``crm_sim_halo_pack`` ... ``crm_sim_apply_divisions``), the transport through ``torch.distributed``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+HEADER_BYTES = 64  # message header: int32 n_records, float32 max_extent
+
+
+# --------------------------------------------------------------------------------------------
+# host logic (numpy only)
+
+class SlabPartition:
+    """Ownership intervals along x: rank r owns centroid x in [edges[r], edges[r+1]); the outer
+    edges are -inf/+inf so that every rod has an owner."""
+
+    def __init__(self, inner_edges):
+        inner = np.asarray(inner_edges, dtype=np.float32)
+        if np.any(np.diff(inner) <= 0):
+            raise ValueError("slab edges must increase")
+        self.edges = np.concatenate([[-np.inf], inner, [np.inf]]).astype(np.float32)
+
+    @property
+    def world(self) -> int:
+        return len(self.edges) - 1
+
+    @classmethod
+    def uniform(cls, domain_x: float, world: int) -> "SlabPartition":
+        return cls(np.linspace(0.0, float(domain_x), world + 1)[1:-1])
+
+    @classmethod
+    def balanced(cls, centroid_x, world: int) -> "SlabPartition":
+        """Equal rod counts per slab (weak scaling): edges at the quantiles of the centroids."""
+        cx = np.sort(np.asarray(centroid_x, dtype=np.float64))
+        if world == 1 or len(cx) == 0:
+            return cls([])
+        cuts = [(cx[min(len(cx) - 1, (len(cx) * r) // world)] + cx[max(0, (len(cx) * r) // world - 1)]) / 2
+                for r in range(1, world)]
+        return cls(np.maximum.accumulate(np.asarray(cuts)) + np.arange(world - 1) * 1e-3)
+
+    def owner(self, centroid_x) -> np.ndarray:
+        """Same rule as the device (``x >= lo && x < hi`` on the f32 centroid)."""
+        cx = np.asarray(centroid_x, dtype=np.float32)
+        return np.searchsorted(self.edges[1:-1], cx, side="right").astype(np.int64)
+
+    def bounds(self, rank: int):
+        return float(self.edges[rank]), float(self.edges[rank + 1])
+
+    def min_width(self) -> float:
+        inner = self.edges[1:-1]
+        return float(np.min(np.diff(inner))) if len(inner) > 1 else float("inf")
+
+
+def centroid_x(pos) -> np.ndarray:
+    """f32 centroid x of every rod as the device computes it (sum of the vertices * 1/Nv)."""
+    pos = np.asarray(pos, dtype=np.float32)
+    return (pos[:, :, 0].sum(axis=1, dtype=np.float32) * np.float32(1.0 / pos.shape[1])).astype(np.float32)
+
+
+def assign_division_ids(per_rank, vox_counter: np.ndarray, n_total: int):
+    """Identifiers of one division step from the division lists of all slabs.
+
+    ``per_rank[r] = (gslot_mother[], user_voxel[])``.  Mirrors the unsharded bookkeeping
+    (csrc/crm_sim.cu handle_divisions; cellular_raza update_cell_cycle): mothers ordered by global
+    slot; inside a voxel the mothers are renamed first (counter+1+k), then the new cells
+    (counter+count+1+k); daughter k of the step gets global slot n_total+k.  Updates
+    ``vox_counter`` in place and returns ``per_rank`` lists of (id_mother, id_daughter,
+    gslot_daughter) in each rank's own order."""
+    gs = np.concatenate([np.asarray(g, dtype=np.uint64) for g, _ in per_rank]) if per_rank else np.zeros(0, np.uint64)
+    vx = np.concatenate([np.asarray(v, dtype=np.int64) for _, v in per_rank]) if per_rank else np.zeros(0, np.int64)
+    order = np.argsort(gs, kind="stable")
+    n = len(gs)
+    rank_in_step = np.empty(n, dtype=np.int64)
+    rank_in_step[order] = np.arange(n)
+    per_vox = np.bincount(vx, minlength=len(vox_counter)).astype(np.uint64)
+    k_in_vox = np.empty(n, dtype=np.uint64)
+    seen = {}
+    for i in order:
+        v = int(vx[i])
+        k_in_vox[i] = seen.get(v, 0)
+        seen[v] = seen.get(v, 0) + 1
+    idm = np.zeros(n, dtype=_capi.IDENT_DTYPE)
+    idd = np.zeros(n, dtype=_capi.IDENT_DTYPE)
+    idm["kind"] = idd["kind"] = _capi.ID_DIVISION
+    idm["voxel"] = idd["voxel"] = vx.astype(np.uint64)
+    base = vox_counter[vx].astype(np.uint64)
+    idm["counter"] = base + np.uint64(1) + k_in_vox
+    idd["counter"] = base + per_vox[vx] + np.uint64(1) + k_in_vox
+    gsd = (np.uint64(n_total) + rank_in_step.astype(np.uint64)).astype(np.uint64)
+    vox_counter += (2 * per_vox).astype(vox_counter.dtype)
+    out, o = [], 0
+    for g, _ in per_rank:
+        m = len(g)
+        out.append((idm[o:o + m].copy(), idd[o:o + m].copy(), gsd[o:o + m].copy()))
+        o += m
+    return out
+
+
+def merge_snapshots(per_rank):
+    """``per_rank[r]`` = list of (iteration, pos, vel, par, ids, parents, gslot) -> one list of
+    (iteration, pos, vel, par, ids, parents) with the rods in global-slot order, i.e. exactly the
+    slot order of the unsharded run."""
+    n_snap = len(per_rank[0])
+    out = []
+    for k in range(n_snap):
+        it = per_rank[0][k][0]
+        assert all(p[k][0] == it for p in per_rank), "ranks disagree on the save iterations"
+        parts = [p[k] for p in per_rank if len(p[k][6])]
+        if not parts:
+            parts = [per_rank[0][k]]
+        gs = np.concatenate([p[6] for p in parts])
+        order = np.argsort(gs, kind="stable")
+        out.append((it,) + tuple(np.concatenate([p[j] for p in parts])[order] for j in range(1, 6)))
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# one slab on one device
+
+class Shard:
+    """Device side of one slab: a ``crm_sim`` in sharded mode plus its exchange buffers."""
+
+    def __init__(self, lib, cfg, device: int, rank: int, partition: SlabPartition, halo_cap: int = 0):
+        import torch
+
+        self.torch = torch
+        self.lib, self.cfg, self.rank, self.partition = lib, cfg, rank, partition
+        self.device = torch.device("cuda", device)
+        self.sim = _capi.Sim(lib, cfg, device)
+        lo, hi = partition.bounds(rank)
+        lib.check(lib.fn("sim_set_slab")(self.sim.h, lo, hi))
+        self.halo_cap = halo_cap
+        self.msg = None
+        self.emax_nb = 0.0
+
+    def close(self):
+        self.sim.close()
+
+    # -- setup ---------------------------------------------------------------
+    def set_agents(self, pos, vel, par, gslots):
+        L, h = self.lib, self.sim.h
+        self.sim.set_agents(pos, vel, par)
+        gs = np.ascontiguousarray(gslots, dtype=np.uint64)
+        L.check(L.fn("sim_set_global_slots")(h, gs.ctypes.data_as(C.c_void_p), len(gs)))
+        self.rb = int(L.fn("sim_halo_record_bytes")(h))
+        self.mb = int(L.fn("sim_migrant_record_bytes")(h))
+        if not self.halo_cap:
+            self.halo_cap = max(4096, len(gs) // 8)
+        t = self.torch
+        self.send = [t.zeros(HEADER_BYTES + self.halo_cap * self.rb, dtype=t.uint8, device=self.device) for _ in range(2)]
+        self.recv = [t.zeros_like(self.send[0]) for _ in range(2)]
+
+    @property
+    def n_rods(self):
+        return self.sim.n_rods
+
+    def max_extent(self) -> float:
+        return float(self.lib.fn("sim_max_extent")(self.sim.h))
+
+    def halo_width(self, emax_global: float) -> float:
+        """A rod interacts with rods whose centroid is at most ext_a + ext_b + range away."""
+        r = float(self.lib.fn("sim_search_radius")(self.sim.h))
+        return (self.max_extent() + emax_global) * 1.02 + r * 1.02 + 1e-3
+
+    # -- halo ----------------------------------------------------------------
+    def pack(self, emax_global: float):
+        """Fills the two send messages (towards the lower / upper neighbour)."""
+        L, h, t = self.lib, self.sim.h, self.torch
+        width = self.halo_width(emax_global)
+        for side in (0, 1):
+            n = C.c_uint32(0)
+            nb = self.rank - 1 if side == 0 else self.rank + 1
+            if 0 <= nb < self.partition.world:
+                L.check(L.fn("sim_halo_pack")(h, side, width, C.c_void_p(self.send[side].data_ptr() + HEADER_BYTES),
+                                              self.halo_cap, C.byref(n)))
+            hdr = np.zeros(2, dtype=np.int32)
+            hdr[0] = n.value
+            hdr[1:2].view(np.float32)[0] = self.max_extent()
+            self.send[side][:8].copy_(t.from_numpy(hdr.view(np.uint8)))
+        return self.send
+
+    def receive(self, have_lo: bool, have_hi: bool):
+        """Installs the received messages (``self.recv``) as ghost rods."""
+        L, h = self.lib, self.sim.h
+        counts, emax = [0, 0], 0.0
+        for side, have in ((0, have_lo), (1, have_hi)):
+            if have:
+                hdr = self.recv[side][:8].cpu().numpy().view(np.int32)
+                counts[side] = int(hdr[0])
+                emax = max(emax, float(hdr[1:2].view(np.float32)[0]))
+        self.emax_nb = emax
+        L.check(L.fn("sim_set_ghosts")(h, C.c_void_p(self.recv[0].data_ptr() + HEADER_BYTES), counts[0],
+                                       C.c_void_p(self.recv[1].data_ptr() + HEADER_BYTES), counts[1], emax))
+        return counts
+
+    # -- step ----------------------------------------------------------------
+    def step_local(self):
+        self.sim.step(1)
+        n_div = int(self.lib.fn("sim_pending_divisions")(self.sim.h, None, None, 0))
+        n_leave = int(self.lib.fn("sim_n_leaving")(self.sim.h))
+        return n_div, n_leave
+
+    def pending_divisions(self):
+        L, h = self.lib, self.sim.h
+        n = int(L.fn("sim_pending_divisions")(h, None, None, 0))
+        gs = np.zeros(n, dtype=np.uint64)
+        vx = np.zeros(n, dtype=np.uint32)
+        L.fn("sim_pending_divisions")(h, gs.ctypes.data_as(C.c_void_p), vx.ctypes.data_as(C.c_void_p), n)
+        return gs, vx
+
+    def apply_divisions(self, idm, idd, gsd):
+        L = self.lib
+        idm, idd = np.ascontiguousarray(idm), np.ascontiguousarray(idd)
+        gsd = np.ascontiguousarray(gsd, dtype=np.uint64)
+        L.check(L.fn("sim_apply_divisions")(self.sim.h, idm.ctypes.data_as(C.c_void_p), idd.ctypes.data_as(C.c_void_p),
+                                            gsd.ctypes.data_as(C.c_void_p), len(gsd)))
+
+    # -- migration -------------------------------------------------------------
+    def migrate_out(self, cap: int = 4096):
+        """Returns two uint8 host arrays (records for the lower / upper neighbour)."""
+        L, h = self.lib, self.sim.h
+        bufs = [np.zeros(cap * self.mb, dtype=np.uint8) for _ in range(2)]
+        n_lo, n_hi = C.c_uint32(0), C.c_uint32(0)
+        L.check(L.fn("sim_migrate_out")(h, bufs[0].ctypes.data_as(C.c_void_p), cap, C.byref(n_lo),
+                                        bufs[1].ctypes.data_as(C.c_void_p), cap, C.byref(n_hi)))
+        return bufs[0][:n_lo.value * self.mb], bufs[1][:n_hi.value * self.mb]
+
+    def migrate_in(self, records: np.ndarray):
+        n = len(records) // self.mb
+        if n:
+            rec = np.ascontiguousarray(records)
+            self.lib.check(self.lib.fn("sim_migrate_in")(self.sim.h, rec.ctypes.data_as(C.c_void_p), n))
+
+    # -- results ---------------------------------------------------------------
+    def take_snapshot(self):
+        self.lib.check(self.lib.fn("sim_take_snapshot")(self.sim.h))
+
+    def snapshots(self):
+        out = []
+        for k, s in enumerate(self.sim.snapshots()):
+            gs = np.zeros(len(s[1]), dtype=np.uint64)
+            self.lib.check(self.lib.fn("sim_snapshot_global_slots")(self.sim.h, k, gs.ctypes.data_as(C.c_void_p)))
+            out.append(s + (gs,))
+        return out
+
+    def global_slots(self):
+        gs = np.zeros(self.n_rods, dtype=np.uint64)
+        self.lib.fn("sim_get_global_slots")(self.sim.h, gs.ctypes.data_as(C.c_void_p))
+        return gs
+
+
+def split_agents(partition: SlabPartition, pos, vel, par):
+    """Per-rank (pos, vel, par, gslots) of an agent list given in global-slot order."""
+    owner = partition.owner(centroid_x(pos)) if len(pos) else np.zeros(0, np.int64)
+    out = []
+    for r in range(partition.world):
+        idx = np.nonzero(owner == r)[0]
+        out.append((pos[idx], vel[idx], par[idx], idx.astype(np.uint64)))
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# drivers
+
+class _Coordinator:
+    """State every rank replicates: per-voxel identifier counters and the global rod count."""
+
+    def __init__(self, cfg, n_total: int):
+        self.vox_counter = np.zeros(int(cfg.n_voxels[0]) * int(cfg.n_voxels[1]), dtype=np.uint64)
+        self.n_total = int(n_total)
+
+    def divisions(self, per_rank):
+        res = assign_division_ids(per_rank, self.vox_counter, self.n_total)
+        self.n_total += sum(len(g) for g, _ in per_rank)
+        return res
+
+
+class LocalCluster:
+    """All slabs in ONE process (several sims on one or more devices); the transport is a tensor
+    copy.  Used by the tests to exercise halo exchange, migration and division bookkeeping on a
+    single GPU, and as the reference for the distributed driver's protocol."""
+
+    def __init__(self, lib, cfg, partition: SlabPartition, devices=None, halo_cap: int = 0):
+        w = partition.world
+        devices = devices or [0] * w
+        self.cfg, self.partition = cfg, partition
+        self.shards = [Shard(lib, cfg, devices[r], r, partition, halo_cap) for r in range(w)]
+        self.coord = None
+        self.iteration = 0
+
+    def close(self):
+        for s in self.shards:
+            s.close()
+
+    def set_agents(self, pos, vel, par):
+        for s, part in zip(self.shards, split_agents(self.partition, pos, vel, par)):
+            s.set_agents(*part)
+        self.coord = _Coordinator(self.cfg, len(pos))
+        self._migrate()  # nothing moves, but it validates the partition
+
+    def _emax(self):
+        return max(s.max_extent() for s in self.shards)
+
+    def _exchange_halos(self):
+        emax = self._emax()
+        w = len(self.shards)
+        for s in self.shards:
+            s.pack(emax)
+        for r, s in enumerate(self.shards):
+            if r > 0:
+                s.recv[0].copy_(self.shards[r - 1].send[1])
+            if r + 1 < w:
+                s.recv[1].copy_(self.shards[r + 1].send[0])
+        for r, s in enumerate(self.shards):
+            s.receive(r > 0, r + 1 < w)
+
+    def _migrate(self):
+        w = len(self.shards)
+        outs = [s.migrate_out() for s in self.shards]
+        for r, s in enumerate(self.shards):
+            if r > 0:
+                s.migrate_in(outs[r - 1][1])
+            if r + 1 < w:
+                s.migrate_in(outs[r + 1][0])
+
+    def step(self, n_steps: int = 1):
+        for _ in range(n_steps):
+            self._exchange_halos()
+            status = [s.step_local() for s in self.shards]
+            self.iteration += 1
+            if any(nd for nd, _ in status):
+                res = self.coord.divisions([s.pending_divisions() for s in self.shards])
+                for s, r in zip(self.shards, res):
+                    s.apply_divisions(*r)
+            if any(nl for _, nl in status):
+                self._migrate()
+
+    def compute_forces(self):
+        """Forces / neighbour counts of the current state in global-slot order."""
+        self._exchange_halos()
+        parts = [s.sim.compute_forces() + (s.global_slots(),) for s in self.shards]
+        gs = np.concatenate([p[2] for p in parts])
+        order = np.argsort(gs, kind="stable")
+        return np.concatenate([p[0] for p in parts])[order], np.concatenate([p[1] for p in parts])[order]
+
+    def run(self):
+        its, n_it = self.shards[0].lib.save_schedule(self.cfg)
+        saves = set(int(i) for i in its)
+        if 0 in saves:
+            for s in self.shards:
+                s.take_snapshot()
+        while self.iteration < n_it:
+            self.step(1)
+            if self.iteration in saves:
+                for s in self.shards:
+                    s.take_snapshot()
+        return merge_snapshots([s.snapshots() for s in self.shards])
+
+    def get_state(self):
+        parts = [s.sim.get_state() + (s.global_slots(),) for s in self.shards]
+        order = np.argsort(np.concatenate([p[5] for p in parts]), kind="stable")
+        return tuple(np.concatenate([p[j] for p in parts])[order] for j in range(5))
+
+
+class Transport:
+    """Neighbour send/recv and small collectives over ``torch.distributed`` (NCCL for cuda tensors,
+    gloo for the CPU tests of the host protocol)."""
+
+    def __init__(self, device, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.group, self.device = torch, dist, group, torch.device(device)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def neighbours(self):
+        return (self.rank - 1 if self.rank > 0 else None, self.rank + 1 if self.rank + 1 < self.world else None)
+
+    def sendrecv(self, send, recv):
+        """send[0]/recv[0] <-> lower neighbour, send[1]/recv[1] <-> upper neighbour; empty tensors
+        are skipped (both sides know the sizes)."""
+        dist, ops = self.dist, []
+        for side, nb in enumerate(self.neighbours()):
+            if nb is None:
+                continue
+            if send[side].numel():
+                ops.append(dist.P2POp(dist.isend, send[side], nb, group=self.group))
+            if recv[side].numel():
+                ops.append(dist.P2POp(dist.irecv, recv[side], nb, group=self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            if self.device.type == "cuda":
+                self.torch.cuda.current_stream(self.device).synchronize()
+
+    def allgather(self, values) -> np.ndarray:
+        t = self.torch.tensor(values, dtype=self.torch.float64, device=self.device)
+        out = [self.torch.zeros_like(t) for _ in range(self.world)]
+        self.dist.all_gather(out, t, group=self.group)
+        return self.torch.stack(out).cpu().numpy()
+
+    def gather_divisions(self, gs, vx, counts):
+        """Division lists (global slot of the mother, user voxel) of all ranks."""
+        t = self.torch
+        m = int(max(counts))
+        buf = np.zeros((m, 2), dtype=np.int64)
+        buf[:len(gs), 0] = np.asarray(gs).astype(np.int64)
+        buf[:len(gs), 1] = vx
+        mine = t.from_numpy(buf).to(self.device)
+        out = [t.zeros_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(out, mine, group=self.group)
+        out = [o.cpu().numpy() for o in out]
+        return [(out[r][:int(counts[r]), 0].astype(np.uint64), out[r][:int(counts[r]), 1]) for r in range(self.world)]
+
+    def exchange_records(self, out, record_bytes: int):
+        """Variable-length byte records to both neighbours: counts first, then the payload."""
+        t = self.torch
+        cs = [t.tensor([len(o) // record_bytes], dtype=t.int64, device=self.device) for o in out]
+        cr = [t.zeros(1, dtype=t.int64, device=self.device) for _ in range(2)]
+        self.sendrecv(cs, cr)
+        send = [t.from_numpy(np.ascontiguousarray(o)).to(self.device) for o in out]
+        recv = [t.zeros(int(c.item()) * record_bytes, dtype=t.uint8, device=self.device) for c in cr]
+        self.sendrecv(send, recv)
+        return [r.cpu().numpy() for r in recv]
+
+
+class DistributedShard:
+    """One slab per process; transport = ``torch.distributed`` (NCCL on GPUs).  Every rank calls
+    the same methods in the same order."""
+
+    def __init__(self, lib, cfg, partition: SlabPartition, device: int, halo_cap: int = 0, group=None):
+        import torch
+
+        self.tr = Transport(torch.device("cuda", device), group)
+        self.rank, self.world = self.tr.rank, self.tr.world
+        if partition.world != self.world:
+            raise ValueError("partition and process group disagree on the number of slabs")
+        self.cfg, self.partition = cfg, partition
+        self.shard = Shard(lib, cfg, device, self.rank, partition, halo_cap)
+        self.iteration = 0
+        self.coord = None
+        self.emax_global = 0.0
+
+    def close(self):
+        self.shard.close()
+
+    def set_agents_local(self, pos, vel, par, gslots, n_total: int):
+        self.shard.set_agents(pos, vel, par, gslots)
+        self.coord = _Coordinator(self.cfg, n_total)
+        self.emax_global = float(self.tr.allgather([self.shard.max_extent()]).max())
+        need = 2.0 * self.shard.halo_width(self.emax_global)
+        if self.partition.min_width() < need:
+            raise ValueError(f"slabs narrower than two halo widths ({need:.1f} um): use fewer GPUs")
+
+    def set_agents(self, pos, vel, par):
+        part = split_agents(self.partition, pos, vel, par)[self.rank]
+        self.set_agents_local(*part, n_total=len(pos))
+
+    def _exchange_halos(self):
+        s = self.shard
+        s.pack(self.emax_global)
+        lo, hi = self.tr.neighbours()
+        self.tr.sendrecv(s.send, s.recv)
+        s.receive(lo is not None, hi is not None)
+        self.emax_global = max(self.emax_global, s.emax_nb)
+
+    def _migrate(self):
+        s = self.shard
+        for r in self.tr.exchange_records(s.migrate_out(), s.mb):
+            s.migrate_in(r)
+
+    def step(self, n_steps: int = 1):
+        for _ in range(n_steps):
+            self._exchange_halos()
+            n_div, n_leave = self.shard.step_local()
+            self.iteration += 1
+            st = self.tr.allgather([n_div, n_leave, self.shard.max_extent()])
+            self.emax_global = float(st[:, 2].max())
+            if st[:, 0].sum() > 0:
+                gs, vx = self.shard.pending_divisions()
+                res = self.coord.divisions(self.tr.gather_divisions(gs, vx, st[:, 0].astype(np.int64)))
+                self.shard.apply_divisions(*res[self.rank])
+            if st[:, 1].sum() > 0:
+                self._migrate()
+
+    def run(self):
+        """Steps to t_max; returns the merged snapshots on every rank."""
+        its, n_it = self.shard.lib.save_schedule(self.cfg)
+        saves = set(int(i) for i in its)
+        if 0 in saves:
+            self.shard.take_snapshot()
+        while self.iteration < n_it:
+            self.step(1)
+            if self.iteration in saves:
+                self.shard.take_snapshot()
+        mine = self.shard.snapshots()
+        gathered = [None] * self.world
+        self.tr.dist.all_gather_object(gathered, mine, group=self.tr.group)
+        return merge_snapshots(gathered)

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CRM_ABI_VERSION 1
+#define CRM_ABI_VERSION 2
 
 typedef enum crm_status {
     CRM_OK = 0,
@@ -190,6 +190,50 @@ uint64_t crm_sim_rod_steps(const crm_sim* sim);
 int crm_sim_enable_timers(crm_sim* sim, int enable);
 int crm_sim_read_timers(crm_sim* sim, double* force_ms, uint64_t* force_launches,
                         uint64_t* last_pairs_in_cutoff, uint64_t* last_pairs_tested);
+
+/* ---- voxel-slab sharding over several GPUs ------------------------------
+ * Replaces the sub-domain machinery of the reference backend: `Configuration.n_threads`
+ * sub-domains of voxels that exchange boundary-voxel agents and returned forces every step
+ * (reference src/simulation.rs:251-256,283-292; cellular_raza chili SubDomainBox).  One crm_sim
+ * per GPU owns the rods whose centroid x lies in [x_lo, x_hi).  Forces are gathered by the owner,
+ * so one exchange of halo records per step replaces the reference's position + force round trip.
+ * The transport (NCCL send/recv, or a plain copy between two sims of one device in the tests)
+ * lives above the ABI; `dev_*` arguments are DEVICE pointers owned by the caller. */
+/* Declare the slab and switch the sim to sharded mode: divisions are deferred to
+ * crm_sim_apply_divisions because identifiers depend on the divisions of all slabs. */
+int crm_sim_set_slab(crm_sim* sim, float x_lo, float x_hi);
+/* Global slot of every owned rod = its slot in the unsharded run (index in the input list for
+ * initial rods): the partition-independent ordering key of divisions and snapshots. */
+int crm_sim_set_global_slots(crm_sim* sim, const uint64_t* gslots, uint32_t n);
+int crm_sim_get_global_slots(const crm_sim* sim, uint64_t* out);
+uint32_t crm_sim_halo_record_bytes(const crm_sim* sim);
+uint32_t crm_sim_migrant_record_bytes(const crm_sim* sim);
+float crm_sim_max_extent(const crm_sim* sim);    /* max centroid->vertex distance over owned rods */
+float crm_sim_search_radius(const crm_sim* sim); /* max interaction range over owned rods */
+/* Halo records of the owned rods whose centroid lies within `width` of the lower (side 0) /
+ * upper (side 1) slab edge, in slot order, into dev_buf (capacity `cap` records). */
+int crm_sim_halo_pack(crm_sim* sim, int side, float width, void* dev_buf, uint32_t cap, uint32_t* n);
+/* Replace the ghost rods by the records received from the lower / upper neighbour;
+ * max_extent = the largest extent among them (as reported by their owners). */
+int crm_sim_set_ghosts(crm_sim* sim, const void* dev_lo, uint32_t n_lo, const void* dev_hi, uint32_t n_hi,
+                       float max_extent);
+/* Migration (the reference re-sorts agents into voxels / sub-domains after every step): remove the
+ * owned rods whose centroid left the slab and write their full records (device state, parameters,
+ * identifier, parent, global slot) into HOST buffers; append received records as owned rods. */
+/* Owned rods whose centroid was outside the slab after the last step (counted by the integrator). */
+uint32_t crm_sim_n_leaving(const crm_sim* sim);
+int crm_sim_migrate_out(crm_sim* sim, void* host_lo, uint32_t cap_lo, uint32_t* n_lo, void* host_hi, uint32_t cap_hi,
+                        uint32_t* n_hi);
+int crm_sim_migrate_in(crm_sim* sim, const void* host_buf, uint32_t n);
+/* Divisions of the last step in sharded mode: (global slot of the mother, user voxel) ordered by
+ * global slot; the coordinator merges the lists of all slabs, derives the identifiers
+ * (cellular_raza update_cell_cycle: per-voxel counter) and hands them back. */
+uint32_t crm_sim_pending_divisions(const crm_sim* sim, uint64_t* gslot_mother, uint32_t* user_voxel, uint32_t cap);
+int crm_sim_apply_divisions(crm_sim* sim, const crm_ident* id_mother, const crm_ident* id_daughter,
+                            const uint64_t* gslot_daughter, uint32_t n);
+/* Snapshot of the owned rods now (sharded runs are stepped by the coordinator, not crm_sim_run). */
+int crm_sim_take_snapshot(crm_sim* sim);
+int crm_sim_snapshot_global_slots(const crm_sim* sim, uint32_t k, uint64_t* out);
 
 /* Non-tensor peaks of the device the force kernel is bounded by (not in the driver's
  * MEASURED_PEAKS.json): dense FP32 FMA TFLOP/s, MUFU.EX2 Top/s, and the SM clock the FMA
