@@ -181,15 +181,6 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_mod
-
-        torch.cuda.set_device(local_rank)
-        dist_mod.init_process_group("nccl")
-        dist = dist_mod
-
     lib = _capi.product()
     ndev = lib.fn("device_count")()
     if ndev <= 0:
@@ -197,64 +188,122 @@ def main():
     device = local_rank % ndev
     W = max(args.warmup, 3)
     K = args.steps
-
-    cfg, pos, par = workload(args.rods, seed=12345 + rank)
-    vel = np.zeros_like(pos)
-    n = len(pos)
+    import ctypes as C
 
     # non-tensor peaks of this device (not in MEASURED_PEAKS.json)
-    import ctypes as C
     fp32, mufu, mhz = C.c_double(0), C.c_double(0), C.c_double(0)
     lib.check(lib.fn("microbench")(device, C.byref(fp32), C.byref(mufu), C.byref(mhz)))
 
-    def barrier():
-        if dist is not None:
-            import torch
+    if world == 1:
+        cfg, pos, par = workload(args.rods, seed=12345)
+        vel = np.zeros_like(pos)
+        n = len(pos)
+        sim = _capi.Sim(lib, cfg, device)
+        sim.set_agents(pos, vel, par)
+        # interacting ordered pairs of this colony (instrumented launch, outside the timed region)
+        sim.compute_forces()
+        pairs = sim.read_timers()
+        sim.step(W)
+        sim.enable_timers(True)
+        launches0 = sim.launch_count()
+        sampler = ClockSampler(device)
+        sampler.start()
+        ms = sim.step_timed(K)
+        clocks = sampler.stop()
+        launches = sim.launch_count() - launches0
+        tm = sim.read_timers()
+        sim.enable_timers(False)
+        sim.close()
+
+        # e2e: host buffers in, K steps, host buffers out, through the C ABI
+        sim2 = _capi.Sim(lib, cfg, device)
+        t0 = time.perf_counter()
+        sim2.set_agents(pos, vel, par)
+        sim2.step(K)
+        pos_out = sim2.get_state()[0]
+        e2e_s = time.perf_counter() - t0
+        assert np.isfinite(pos_out).all()
+        h2d = pos.nbytes + vel.nbytes + n * (32 + 16 + 16 + 48 + 4)
+        d2h = pos_out.nbytes * 2 + n * 20 + K * 40
+        sim2.close()
+        total_rods = n
+        parallelism = "1 GPU"
+        halo = None
+    else:
+        # one slab of ONE colony per GPU: halo exchange over NCCL every step
+        import torch
+        import torch.distributed as dist
+
+        from cr_mech_coli_b200 import sharded
+        from cr_mech_coli_b200.testing import lattice_slab, mie_params
+
+        torch.cuda.set_device(device)
+        dist.init_process_group("nccl")
+        pos, domain, edges, g0 = lattice_slab(args.rods, rank, world)
+        n = len(pos)
+        nvx = (max(1, int(domain[0] // 40.0)), max(1, int(domain[1] // 40.0)))
+        cfg = _capi.make_config(domain_size=domain, domain_height=2.5, n_voxels=nvx, dt=0.01, t_max=1e6, n_saves=0)
+        par = mie_params(n, growth_rate=0.0)
+        par["spring_length_threshold"] = 1e30
+        vel = np.zeros_like(pos)
+        part = sharded.SlabPartition(edges)
+        gsl = np.arange(g0, g0 + n, dtype=np.uint64)
+
+        def barrier():
             dist.barrier()
             torch.cuda.synchronize()
 
-    sim = _capi.Sim(lib, cfg, device)
-    sim.set_agents(pos, vel, par)
-    # interacting ordered pairs of this colony (instrumented launch, outside the timed region)
-    sim.compute_forces()
-    pairs = sim.read_timers()
-    sim.step(W)
-    sim.enable_timers(True)
-    launches0 = sim.launch_count()
-    sampler = ClockSampler(device)
-    sampler.start()
-    barrier()
-    ms = sim.step_timed(K)
-    barrier()
-    clocks = sampler.stop()
-    launches = sim.launch_count() - launches0
-    tm = sim.read_timers()
-    sim.enable_timers(False)
+        ds = sharded.DistributedShard(lib, cfg, part, device)
+        ds.set_agents_local(pos, vel, par, gsl, n_total=n * world)
+        ds._exchange_halos()
+        ds.shard.sim.compute_forces()
+        pairs = ds.shard.sim.read_timers()
+        halo = {"ghost_rods_rank0": int(sum(ds.shard.receive(*[x is not None for x in ds.tr.neighbours()]))),
+                "record_bytes": ds.shard.rb}
+        ds.step(W)
+        ds.shard.sim.enable_timers(True)
+        launches0 = ds.shard.sim.launch_count()
+        sampler = ClockSampler(device)
+        sampler.start()
+        barrier()
+        lib.check(lib.fn("sim_timer_start")(ds.shard.sim.h))
+        ds.step(K)
+        msd = C.c_double(0)
+        lib.check(lib.fn("sim_timer_stop")(ds.shard.sim.h, C.byref(msd)))
+        barrier()
+        ms = float(msd.value)
+        clocks = sampler.stop()
+        launches = ds.shard.sim.launch_count() - launches0
+        tm = ds.shard.sim.read_timers()
+        ds.close()
 
-    # e2e: host buffers in, K steps, host buffers out, through the C ABI
-    sim2 = _capi.Sim(lib, cfg, device)
-    barrier()
-    t0 = time.perf_counter()
-    sim2.set_agents(pos, vel, par)
-    sim2.step(K)
-    pos_out = sim2.get_state()[0]
-    e2e_s = time.perf_counter() - t0
-    barrier()
-    assert np.isfinite(pos_out).all()
-    h2d = pos.nbytes + vel.nbytes + n * (32 + 16 + 16 + 48 + 4)
-    d2h = pos_out.nbytes * 2 + n * 20 + K * 40
-    sim2.close()
-
-    if dist is not None:
-        import torch
+        # e2e: host buffers in, K sharded steps, host buffers out
+        ds2 = sharded.DistributedShard(lib, cfg, part, device)
+        barrier()
+        t0 = time.perf_counter()
+        ds2.set_agents_local(pos, vel, par, gsl, n_total=n * world)
+        ds2.step(K)
+        pos_out = ds2.shard.sim.get_state()[0]
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        barrier()
+        assert np.isfinite(pos_out).all()
+        h2d = pos.nbytes + vel.nbytes + n * (32 + 16 + 16 + 48 + 4)
+        d2h = pos_out.nbytes * 2 + n * 20 + K * 40
+        ds2.close()
         t = torch.tensor([ms, e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_s = float(t[0]), float(t[1])
-    if rank != 0:
-        return
+        cnt = torch.tensor([n], device="cuda", dtype=torch.int64)
+        dist.all_reduce(cnt)
+        total_rods = int(cnt.item())
+        parallelism = f"{world} voxel slabs along x, one per GPU, per-step NCCL halo exchange"
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return
 
     peaks, peaks_src = measured_peaks()
-    total_rods = n * world
     value = total_rods * K / (ms * 1e-3)
     force_ms = tm["force_ms"] / max(tm["force_launches"], 1)
     flops = pairs["pairs_in_cutoff"] * EVALS_PER_ORDERED_PAIR * FLOP_PER_EVAL["mie"]
@@ -267,12 +316,13 @@ def main():
         "config": {"workload": "C3: 2D monolayer, jittered nematic lattice (24x4 um spacing), Mie n=6 m=3, "
                                "r=1.5, cutoff 6, 8 vertices/rod, dt=0.01, growth 0",
                    "rods_per_gpu": n, "rods_total": total_rods,
-                   "parallelism": "1 GPU" if world == 1 else f"{world} independent slabs (weak)",
+                   "parallelism": parallelism,
                    "l2": "state (~0.9 GB/GPU) larger than the 126 MB L2; no explicit flush",
                    "math": "MUFU fast path (rsqrt/ex2/lg2) + bit-exact closest-point geometry"},
         "e2e": {"value": total_rods * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d / K,
                 "d2h_bytes_per_step": d2h / K, "seconds": e2e_s},
         "gpu_launches": int(launches),
+        "halo": halo,
         "clocks": clocks,
         "roofline": {"kernel": "k_force<8>", "bound": "fp32", "achieved": achieved, "peak": fp32.value,
                      "unit": "TFLOP/s", "frac": achieved / fp32.value if fp32.value else None,

@@ -149,6 +149,8 @@ class Library:
             ),
             "sim_launch_count": (u64, [vp]),
             "sim_step_timed": (C.c_int, [vp, u32, P(C.c_double)]),
+            "sim_timer_start": (C.c_int, [vp]),
+            "sim_timer_stop": (C.c_int, [vp, P(C.c_double)]),
             "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),

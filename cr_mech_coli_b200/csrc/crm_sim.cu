@@ -424,6 +424,8 @@ void crm_sim_destroy(crm_sim* s) {
     if (s->h_status) cudaFreeHost(s->h_status);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev_t0) cudaEventDestroy(s->ev_t0);
+    if (s->ev_t1) cudaEventDestroy(s->ev_t1);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -523,6 +525,29 @@ int crm_sim_step_timed(crm_sim* s, uint32_t n_steps, double* ms_out) {
     cudaEventDestroy(b);
     if (ms_out) *ms_out = ms;
     return rc;
+}
+
+// Device-side stopwatch on the sim's stream for step sequences driven from above the ABI
+// (sharded runs): start records an event, stop records another one and returns the elapsed ms.
+int crm_sim_timer_start(crm_sim* s) {
+    CK(cudaSetDevice(s->device));
+    if (!s->ev_t0) {
+        CK(cudaEventCreate(&s->ev_t0));
+        CK(cudaEventCreate(&s->ev_t1));
+    }
+    CK(cudaEventRecord(s->ev_t0, s->stream));
+    return 0;
+}
+
+int crm_sim_timer_stop(crm_sim* s, double* ms_out) {
+    CK(cudaSetDevice(s->device));
+    if (!s->ev_t0) return fail(CRM_ERR_INVALID, "timer not started");
+    CK(cudaEventRecord(s->ev_t1, s->stream));
+    CK(cudaEventSynchronize(s->ev_t1));
+    float ms = 0.0f;
+    CK(cudaEventElapsedTime(&ms, s->ev_t0, s->ev_t1));
+    if (ms_out) *ms_out = ms;
+    return 0;
 }
 
 int crm_sim_run(crm_sim* s) {

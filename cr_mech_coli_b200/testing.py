@@ -74,13 +74,16 @@ def _apply(p, kw):
 
 def lattice_colony(n_rods: int, domain: float | None = None, n_vertices: int = 8, spring_length: float = 3.0,
                    spacing=(24.0, 4.0), angle_std: float = 0.02, jitter: float = 0.25, seed: int = 12345,
-                   z: float = 1.25, z_jitter: float = 0.0, margin: float = 14.0):
+                   z: float = 1.25, z_jitter: float = 0.0, margin: float = 14.0, _ny: int | None = None):
     """Jittered nematic lattice (C3): rod centres on a (spacing_x, spacing_y) lattice, angle ~
     N(0, angle_std) clipped at 2.5 sigma, uniform jitter; returns pos[n_rods, n_vertices, 3] f32.  If ``domain`` is
     given the lattice is cut to fit a square domain of that edge (with ``margin``)."""
     rng = np.random.default_rng(seed)
     sx, sy = spacing
-    if domain is None:
+    if _ny is not None:
+        ny = _ny
+        nx = int(np.ceil(n_rods / ny))
+    elif domain is None:
         ny = int(np.ceil(np.sqrt(n_rods * sx / sy)))
         nx = int(np.ceil(n_rods / ny))
     else:
@@ -129,3 +132,25 @@ def random_colony(n_rods: int, domain: float, n_vertices: int = 8, spring_length
     pos[:, :, 1] = c[:, 1:2] + t[None, :] * np.sin(a)
     pos[:, :, 2] = height * (0.5 + rng.uniform(-z_spread, z_spread, (n_rods, 1))) + rng.normal(0, 0.01, (n_rods, n_vertices))
     return pos
+
+
+def lattice_slab(n_per_rank: int, rank: int, world: int, spacing=(24.0, 4.0), margin: float = 14.0, seed: int = 12345,
+                 **kw):
+    """Rank ``rank``'s columns of ONE jittered nematic lattice of about ``world * n_per_rank`` rods
+    (weak scaling: every rank holds the same number of whole lattice columns).  Returns
+    (pos, domain_size (Lx, Ly), inner slab edges, first global slot)."""
+    sx, sy = spacing
+    ny = int(np.ceil(np.sqrt(world * n_per_rank * sx / sy)))
+    nxl = int(np.ceil(n_per_rank / ny))
+    n_local = nxl * ny
+    pos = lattice_colony(n_local, spacing=spacing, margin=margin, seed=seed + rank, **_with_ny(kw, ny))
+    pos[:, :, 0] += np.float32(rank * nxl * sx)
+    domain = (float(world * nxl * sx + 2 * margin), float(ny * sy + 2 * margin))
+    edges = [margin + (r * nxl - 0.5) * sx for r in range(1, world)]
+    return pos, domain, edges, rank * n_local
+
+
+def _with_ny(kw, ny):
+    kw = dict(kw)
+    kw["_ny"] = ny
+    return kw

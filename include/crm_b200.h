@@ -155,6 +155,11 @@ int crm_sim_step(crm_sim* sim, uint32_t n_steps);
  * before the first and after the last kernel of the n_steps (ms). */
 int crm_sim_step_timed(crm_sim* sim, uint32_t n_steps, double* ms);
 
+/* Device stopwatch on the sim's own stream around step sequences driven from above the ABI
+ * (sharded runs: halo exchange + crm_sim_step per step): CUDA events, elapsed ms. */
+int crm_sim_timer_start(crm_sim* sim);
+int crm_sim_timer_stop(crm_sim* sim, double* ms);
+
 /* Force accumulators the next step would use, i.e. the reference's
  * interaction + domain force for the current state (cellular_raza
  * update_mechanics_interaction_step_1..3 + calculate_custom_domain_force).
