@@ -72,17 +72,37 @@ __global__ void k_bin_count(Dev d) {
     d.cell_rank[a] = atomicAdd(&d.cell_count[c], 1u);
 }
 
-// single-block exclusive scan of cell_count -> cell_start (ncells + 1 entries)
-__global__ void k_bin_scan(Dev d, uint32_t ncells) {
+// single-block exclusive scan of cell_count -> cell_start (ncells + 1 entries); every thread owns
+// ITEMS consecutive cells per round (vector loads), so 1e5 cells take a handful of rounds
+__global__ void __launch_bounds__(1024) k_bin_scan(Dev d, uint32_t ncells) {
+    constexpr int ITEMS = 16;
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t carry_s;
     const uint32_t T = blockDim.x;
     if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
-    for (uint32_t base = 0; base < ncells; base += T) {
-        uint32_t i = base + threadIdx.x;
-        uint32_t v = (i < ncells) ? d.cell_count[i] : 0u;
-        uint32_t s = v;
+    for (uint32_t base = 0; base < ncells; base += T * ITEMS) {
+        const uint32_t i0 = base + threadIdx.x * ITEMS;
+        uint32_t v[ITEMS];
+        if (i0 + ITEMS <= ncells) {
+            const uint4* src = reinterpret_cast<const uint4*>(d.cell_count + i0);
+#pragma unroll
+            for (int q = 0; q < ITEMS / 4; ++q) {
+                const uint4 w = src[q];
+                v[4 * q] = w.x; v[4 * q + 1] = w.y; v[4 * q + 2] = w.z; v[4 * q + 3] = w.w;
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < ITEMS; ++q) v[q] = (i0 + q < ncells) ? d.cell_count[i0 + q] : 0u;
+        }
+        uint32_t tot = 0;
+#pragma unroll
+        for (int q = 0; q < ITEMS; ++q) {
+            const uint32_t t = v[q];
+            v[q] = tot;  // exclusive within the thread
+            tot += t;
+        }
+        uint32_t s = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t t = __shfl_up_sync(FULL, s, o);
@@ -101,11 +121,19 @@ __global__ void k_bin_scan(Dev d, uint32_t ncells) {
             warp_tot[threadIdx.x] = ws - w;  // exclusive
         }
         __syncthreads();
-        uint32_t carry = carry_s;
-        uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + s - v;
-        if (i < ncells) d.cell_start[i] = excl;
+        const uint32_t excl = carry_s + warp_tot[threadIdx.x >> 5] + s - tot;
+        if (i0 + ITEMS <= ncells) {
+            uint4* dst = reinterpret_cast<uint4*>(d.cell_start + i0);
+#pragma unroll
+            for (int q = 0; q < ITEMS / 4; ++q)
+                dst[q] = make_uint4(excl + v[4 * q], excl + v[4 * q + 1], excl + v[4 * q + 2], excl + v[4 * q + 3]);
+        } else {
+#pragma unroll
+            for (int q = 0; q < ITEMS; ++q)
+                if (i0 + q < ncells) d.cell_start[i0 + q] = excl + v[q];
+        }
         __syncthreads();
-        if (threadIdx.x == T - 1) carry_s = excl + v;
+        if (threadIdx.x == T - 1) carry_s = excl + tot;
         __syncthreads();
     }
     if (threadIdx.x == 0) d.cell_start[ncells] = carry_s;
@@ -233,13 +261,20 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     // Adams-Bashforth over the stored increments
     const int nh = d.nhist[a];
     const float dt = d.dt;
+    // increment history as a two-slot ring: the slot written two steps ago is read (as the older
+    // increment) and then overwritten with this step's increment
+    const bool odd = (d.iteration & 1ull) != 0;
+    float* const newx = odd ? d.dx2 : d.dx1;  // written at step it-1
+    float* const newv = odd ? d.dv2 : d.dv1;
+    float* const oldx = odd ? d.dx1 : d.dx2;  // written at step it-2, rewritten now
+    float* const oldv = odd ? d.dv1 : d.dv2;
     const float c23 = 23.0f / 12.0f, c16 = 16.0f / 12.0f, c5 = 5.0f / 12.0f;
     const float amp = (diffusion > 0.0f) ? sqrtf(2.0f * diffusion * dt) : 0.0f;
     float Pnew[3], Vnew[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         const size_t i = o + c * LP + li;
-        float x1 = d.dx1[i], v1 = d.dv1[i], x2 = d.dx2[i], v2 = d.dv2[i];
+        float x1 = newx[i], v1 = newv[i], x2 = oldx[i], v2 = oldv[i];
         float ip, iv;
         if (nh >= 2) {
             ip = (c23 * V[c] - c16 * x1 + c5 * x2) * dt;
@@ -257,8 +292,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             ip += amp * n0;
         }
         if (hv) {
-            d.dx2[i] = x1; d.dv2[i] = v1;
-            d.dx1[i] = V[c]; d.dv1[i] = dv[c];
+            oldx[i] = V[c]; oldv[i] = dv[c];
         }
         Pnew[c] = P[c] + ip;
         Vnew[c] = V[c] + iv;

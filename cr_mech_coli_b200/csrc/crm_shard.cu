@@ -44,6 +44,13 @@ __global__ void k_halo_gather(Dev d, const uint32_t* __restrict__ sel, uint32_t 
     out[(size_t)i * rq + q] = v;
 }
 
+// message header (first 64 B of an exchange buffer): {n_records, max_extent bits, flags}
+__global__ void k_write_header(uint32_t* hdr, const uint32_t* count, float emax, uint32_t flags) {
+    hdr[0] = *count;
+    hdr[1] = __float_as_uint(emax);
+    hdr[2] = flags;
+}
+
 // inverse: record i of `in` becomes slot first + i
 __global__ void k_ghost_scatter(Dev d, const float4* __restrict__ in, uint32_t n_rec, uint32_t first, int lp) {
     const int rq = lp + 5;
@@ -235,6 +242,105 @@ int crm_sim_set_ghosts(crm_sim* s, const void* dev_lo, uint32_t n_lo, const void
     CK(cudaStreamSynchronize(s->stream));  // the receive buffers may be reused by the caller
     s->n_ghost = n_lo + n_hi;
     s->emax_ghost = max_extent;
+    return 0;
+}
+
+
+// Both halo messages of a step in one call: [64-byte header {n, max_extent, flags} | records].
+// One stream synchronisation; the counts come back for the caller's bookkeeping.
+int crm_sim_halo_pack_msgs(crm_sim* s, float width, void* dev_msg_lo, void* dev_msg_hi, uint32_t cap,
+                           uint32_t flags, uint32_t* n_lo, uint32_t* n_hi) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    uint32_t n[2] = {0, 0};
+    void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    for (int side = 0; side < 2; ++side) {
+        if (!msg[side]) continue;
+        const float lo = side == 0 ? -INFINITY : s->slab_hi - width;
+        const float hi = side == 0 ? s->slab_lo + width : INFINITY;
+        int rc = select_band(s, lo, hi, &n[side]);
+        if (rc) return rc;
+        if (n[side] > cap)
+            return crm_fail(CRM_ERR_NOMEM, "halo of %u rods exceeds the exchange buffer (%u records)", n[side], cap);
+        if (!s->select_count) CK(cudaMalloc(&s->select_count, sizeof(uint32_t)));
+        if (s->n == 0) CK(cudaMemsetAsync(s->select_count, 0, sizeof(uint32_t), s->stream));
+        k_write_header<<<1, 1, 0, s->stream>>>((uint32_t*)msg[side], s->select_count, s->emax, flags);
+        if (n[side]) {
+            const uint64_t threads = (uint64_t)n[side] * (s->lp + 5);
+            k_halo_gather<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
+                s->d, s->select_out, n[side], s->lp, reinterpret_cast<float4*>((char*)msg[side] + 64));
+        }
+        s->launches += 3;
+    }
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s->stream));  // the transport above the ABI runs on other streams
+    if (n_lo) *n_lo = n[0];
+    if (n_hi) *n_hi = n[1];
+    return 0;
+}
+
+// Halo records of the owned rods whose centroid is OUTSIDE the slab (about to migrate): the old
+// owner keeps them as ghosts for the step in which the new owner has not announced them yet.
+int crm_sim_pack_leavers(crm_sim* s, void* dev_buf, uint32_t cap, uint32_t* n_out) {
+    if (!s || !n_out) return crm_fail(CRM_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    uint32_t total = 0;
+    for (int side = 0; side < 2; ++side) {
+        if ((side == 0 && !(s->slab_lo > -INFINITY)) || (side == 1 && !(s->slab_hi < INFINITY))) continue;
+        uint32_t n = 0;
+        int rc = select_band(s, side == 0 ? -INFINITY : s->slab_hi, side == 0 ? s->slab_lo : INFINITY, &n);
+        if (rc) return rc;
+        if (total + n > cap) return crm_fail(CRM_ERR_NOMEM, "%u leaving rods exceed the buffer", total + n);
+        if (n) {
+            const uint64_t threads = (uint64_t)n * (s->lp + 5);
+            k_halo_gather<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
+                s->d, s->select_out, n, s->lp, reinterpret_cast<float4*>((char*)dev_buf + (size_t)total * (s->lp + 5) * 16));
+            s->launches += 2;
+        }
+        total += n;
+    }
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s->stream));
+    *n_out = total;
+    return 0;
+}
+
+// Install the ghosts of a step from the two received messages (headers read here) plus the
+// caller's own leavers; returns the neighbours' counts, flags and the largest reported extent.
+int crm_sim_set_ghosts_msgs(crm_sim* s, const void* dev_msg_lo, const void* dev_msg_hi, const void* dev_self,
+                            uint32_t n_self, uint32_t* counts, uint32_t* flags, float* max_extent) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null sim");
+    if (s->pending_div) return crm_fail(CRM_ERR_INVALID, "divisions pending");
+    CK(cudaSetDevice(s->device));
+    uint32_t* h = reinterpret_cast<uint32_t*>(s->h_status + 1);  // pinned scratch behind the status block
+    const void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    for (int side = 0; side < 2; ++side) {
+        h[4 * side] = h[4 * side + 1] = h[4 * side + 2] = 0;
+        if (msg[side]) CK(cudaMemcpyAsync(h + 4 * side, msg[side], 12, cudaMemcpyDeviceToHost, s->stream));
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    const uint32_t n_lo = h[0], n_hi = h[4];
+    float emax = std::max(__builtin_bit_cast(float, h[1]), __builtin_bit_cast(float, h[5]));
+    int rc = crm_reserve(s, s->n + n_lo + n_hi + n_self);
+    if (rc) return rc;
+    const uint32_t cnt[3] = {n_lo, n_hi, n_self};
+    const void* src[3] = {msg[0] ? (const char*)msg[0] + 64 : nullptr, msg[1] ? (const char*)msg[1] + 64 : nullptr, dev_self};
+    uint32_t first = s->n;
+    for (int k = 0; k < 3; ++k) {
+        if (!cnt[k]) continue;
+        const uint64_t threads = (uint64_t)cnt[k] * (s->lp + 5);
+        k_ghost_scatter<<<blocks_for(threads, 256), 256, 0, s->stream>>>(s->d, (const float4*)src[k], cnt[k], first, s->lp);
+        first += cnt[k];
+        s->launches += 1;
+    }
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s->stream));  // the receive buffers may be reused by the caller
+    s->n_ghost = n_lo + n_hi + n_self;
+    if (n_self) emax = std::max(emax, s->emax);
+    s->emax_ghost = emax;
+    if (counts) { counts[0] = n_lo; counts[1] = n_hi; }
+    if (flags) { flags[0] = h[2]; flags[1] = h[6]; }
+    if (max_extent) *max_extent = emax;
     return 0;
 }
 

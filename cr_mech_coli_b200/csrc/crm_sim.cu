@@ -392,7 +392,7 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaMalloc(&s->d.status, sizeof(Status)));
     CK(cudaMemset(s->d.status, 0, sizeof(Status)));
-    CK(cudaMallocHost(&s->h_status, sizeof(Status)));
+    CK(cudaMallocHost(&s->h_status, sizeof(Status) + 64));  // + pinned scratch (message headers)
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
     s->d.lx = c->domain_size[0];

@@ -170,6 +170,12 @@ class Shard:
         t = self.torch
         self.send = [t.zeros(HEADER_BYTES + self.halo_cap * self.rb, dtype=t.uint8, device=self.device) for _ in range(2)]
         self.recv = [t.zeros_like(self.send[0]) for _ in range(2)]
+        self.selfbuf = t.zeros(self.halo_cap * self.rb, dtype=t.uint8, device=self.device)
+        self.n_self = 0
+        self.n_leave = 0
+        g = np.asarray(par["growth_rate"]) if len(gs) else np.zeros(0)
+        thr = np.asarray(par["spring_length_threshold"]) if len(gs) else np.zeros(0)
+        self.can_divide = bool(np.any((g != 0) & np.isfinite(thr) & (thr < 1e29)))
 
     @property
     def n_rods(self):
@@ -184,42 +190,47 @@ class Shard:
         return (self.max_extent() + emax_global) * 1.02 + r * 1.02 + 1e-3
 
     # -- halo ----------------------------------------------------------------
-    def pack(self, emax_global: float):
-        """Fills the two send messages (towards the lower / upper neighbour)."""
-        L, h, t = self.lib, self.sim.h, self.torch
-        width = self.halo_width(emax_global)
-        for side in (0, 1):
-            n = C.c_uint32(0)
-            nb = self.rank - 1 if side == 0 else self.rank + 1
-            if 0 <= nb < self.partition.world:
-                L.check(L.fn("sim_halo_pack")(h, side, width, C.c_void_p(self.send[side].data_ptr() + HEADER_BYTES),
-                                              self.halo_cap, C.byref(n)))
-            hdr = np.zeros(2, dtype=np.int32)
-            hdr[0] = n.value
-            hdr[1:2].view(np.float32)[0] = self.max_extent()
-            self.send[side][:8].copy_(t.from_numpy(hdr.view(np.uint8)))
-        return self.send
-
-    def receive(self, have_lo: bool, have_hi: bool):
-        """Installs the received messages (``self.recv``) as ghost rods."""
+    def begin_step(self, emax_nb: float):
+        """Hand over the rods that left the slab during the last step (their halo records stay here
+        as ghosts for this step), then pack both halo messages.  Returns the migrant records
+        (host bytes) for the lower / upper neighbour."""
         L, h = self.lib, self.sim.h
-        counts, emax = [0, 0], 0.0
-        for side, have in ((0, have_lo), (1, have_hi)):
-            if have:
-                hdr = self.recv[side][:8].cpu().numpy().view(np.int32)
-                counts[side] = int(hdr[0])
-                emax = max(emax, float(hdr[1:2].view(np.float32)[0]))
-        self.emax_nb = emax
-        L.check(L.fn("sim_set_ghosts")(h, C.c_void_p(self.recv[0].data_ptr() + HEADER_BYTES), counts[0],
-                                       C.c_void_p(self.recv[1].data_ptr() + HEADER_BYTES), counts[1], emax))
-        return counts
+        out = (np.zeros(0, np.uint8), np.zeros(0, np.uint8))
+        self.n_self = 0
+        if self.n_leave:
+            n = C.c_uint32(0)
+            L.check(L.fn("sim_pack_leavers")(h, C.c_void_p(self.selfbuf.data_ptr()), self.halo_cap, C.byref(n)))
+            self.n_self = int(n.value)
+            out = self.migrate_out()
+            self.n_leave = 0
+        flags = (1 if len(out[0]) else 0) | (2 if len(out[1]) else 0)
+        width = self.halo_width(max(emax_nb, self.max_extent()))
+        lo = C.c_void_p(self.send[0].data_ptr()) if self.rank > 0 else None
+        hi = C.c_void_p(self.send[1].data_ptr()) if self.rank + 1 < self.partition.world else None
+        L.check(L.fn("sim_halo_pack_msgs")(h, width, lo, hi, self.halo_cap, flags, None, None))
+        return out
+
+    def install_ghosts(self):
+        """Ghosts of this step from the received messages + the own leavers.  Returns (counts,
+        incoming-migrant flags per side, largest extent reported by the neighbours)."""
+        L, h = self.lib, self.sim.h
+        lo = C.c_void_p(self.recv[0].data_ptr()) if self.rank > 0 else None
+        hi = C.c_void_p(self.recv[1].data_ptr()) if self.rank + 1 < self.partition.world else None
+        counts = (C.c_uint32 * 2)()
+        flags = (C.c_uint32 * 2)()
+        emax = C.c_float(0)
+        L.check(L.fn("sim_set_ghosts_msgs")(h, lo, hi, C.c_void_p(self.selfbuf.data_ptr()), self.n_self, counts, flags,
+                                            C.byref(emax)))
+        # the lower neighbour announces migrants for us in bit 1 (its upper side), the upper one in bit 0
+        incoming = (bool(flags[0] & 2), bool(flags[1] & 1))
+        return (int(counts[0]), int(counts[1])), incoming, float(emax.value)
 
     # -- step ----------------------------------------------------------------
     def step_local(self):
         self.sim.step(1)
         n_div = int(self.lib.fn("sim_pending_divisions")(self.sim.h, None, None, 0))
-        n_leave = int(self.lib.fn("sim_n_leaving")(self.sim.h))
-        return n_div, n_leave
+        self.n_leave = int(self.lib.fn("sim_n_leaving")(self.sim.h))
+        return n_div, self.n_leave
 
     def pending_divisions(self):
         L, h = self.lib, self.sim.h
@@ -317,32 +328,31 @@ class LocalCluster:
         for s, part in zip(self.shards, split_agents(self.partition, pos, vel, par)):
             s.set_agents(*part)
         self.coord = _Coordinator(self.cfg, len(pos))
-        self._migrate()  # nothing moves, but it validates the partition
-
-    def _emax(self):
-        return max(s.max_extent() for s in self.shards)
+        self.emax_nb = [max(s.max_extent() for s in self.shards)] * len(self.shards)
 
     def _exchange_halos(self):
-        emax = self._emax()
         w = len(self.shards)
-        for s in self.shards:
-            s.pack(emax)
+        outs = [s.begin_step(self.emax_nb[r]) for r, s in enumerate(self.shards)]
         for r, s in enumerate(self.shards):
             if r > 0:
                 s.recv[0].copy_(self.shards[r - 1].send[1])
             if r + 1 < w:
                 s.recv[1].copy_(self.shards[r + 1].send[0])
+        self.shards[0].torch.cuda.synchronize()
         for r, s in enumerate(self.shards):
-            s.receive(r > 0, r + 1 < w)
-
-    def _migrate(self):
-        w = len(self.shards)
-        outs = [s.migrate_out() for s in self.shards]
-        for r, s in enumerate(self.shards):
-            if r > 0:
+            counts, incoming, emax = s.install_ghosts()
+            self.emax_nb[r] = emax
+            got = False
+            if r > 0 and incoming[0]:
+                assert len(outs[r - 1][1])
                 s.migrate_in(outs[r - 1][1])
-            if r + 1 < w:
+                got = True
+            if r + 1 < w and incoming[1]:
+                assert len(outs[r + 1][0])
                 s.migrate_in(outs[r + 1][0])
+                got = True
+            if got:  # the new owned rods took the first ghost slots
+                s.install_ghosts()
 
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
@@ -353,8 +363,6 @@ class LocalCluster:
                 res = self.coord.divisions([s.pending_divisions() for s in self.shards])
                 for s, r in zip(self.shards, res):
                     s.apply_divisions(*r)
-            if any(nl for _, nl in status):
-                self._migrate()
 
     def compute_forces(self):
         """Forces / neighbour counts of the current state in global-slot order."""
@@ -433,14 +441,17 @@ class Transport:
         out = [o.cpu().numpy() for o in out]
         return [(out[r][:int(counts[r]), 0].astype(np.uint64), out[r][:int(counts[r]), 1]) for r in range(self.world)]
 
-    def exchange_records(self, out, record_bytes: int):
-        """Variable-length byte records to both neighbours: counts first, then the payload."""
+    def exchange_records(self, out, record_bytes: int, sides=(True, True)):
+        """Variable-length byte records with the neighbours on the given sides (both ends of a
+        link must pass the same flag): counts first, then the payload."""
         t = self.torch
-        cs = [t.tensor([len(o) // record_bytes], dtype=t.int64, device=self.device) for o in out]
-        cr = [t.zeros(1, dtype=t.int64, device=self.device) for _ in range(2)]
+        e = t.zeros(0, dtype=t.int64, device=self.device)
+        cs = [t.tensor([len(o) // record_bytes], dtype=t.int64, device=self.device) if sd else e for o, sd in zip(out, sides)]
+        cr = [t.zeros(1, dtype=t.int64, device=self.device) if sd else e for sd in sides]
         self.sendrecv(cs, cr)
-        send = [t.from_numpy(np.ascontiguousarray(o)).to(self.device) for o in out]
-        recv = [t.zeros(int(c.item()) * record_bytes, dtype=t.uint8, device=self.device) for c in cr]
+        e8 = t.zeros(0, dtype=t.uint8, device=self.device)
+        send = [t.from_numpy(np.ascontiguousarray(o)).to(self.device) if sd else e8 for o, sd in zip(out, sides)]
+        recv = [t.zeros(int(c.item()) * record_bytes, dtype=t.uint8, device=self.device) if sd else e8 for c, sd in zip(cr, sides)]
         self.sendrecv(send, recv)
         return [r.cpu().numpy() for r in recv]
 
@@ -468,7 +479,9 @@ class DistributedShard:
     def set_agents_local(self, pos, vel, par, gslots, n_total: int):
         self.shard.set_agents(pos, vel, par, gslots)
         self.coord = _Coordinator(self.cfg, n_total)
-        self.emax_global = float(self.tr.allgather([self.shard.max_extent()]).max())
+        st = self.tr.allgather([self.shard.max_extent(), float(self.shard.can_divide)])
+        self.emax_global = float(st[:, 0].max())
+        self.can_divide = bool(st[:, 1].max() > 0)
         need = 2.0 * self.shard.halo_width(self.emax_global)
         if self.partition.min_width() < need:
             raise ValueError(f"slabs narrower than two halo widths ({need:.1f} um): use fewer GPUs")
@@ -479,30 +492,32 @@ class DistributedShard:
 
     def _exchange_halos(self):
         s = self.shard
-        s.pack(self.emax_global)
-        lo, hi = self.tr.neighbours()
+        out = s.begin_step(self.emax_global)
         self.tr.sendrecv(s.send, s.recv)
-        s.receive(lo is not None, hi is not None)
-        self.emax_global = max(self.emax_global, s.emax_nb)
-
-    def _migrate(self):
-        s = self.shard
-        for r in self.tr.exchange_records(s.migrate_out(), s.mb):
-            s.migrate_in(r)
+        counts, incoming, emax = s.install_ghosts()
+        self.last_counts = counts
+        self.emax_global = max(emax, s.max_extent())
+        # migrants travel only between neighbours that announced them in the message headers
+        sides = [bool(len(out[k])) or incoming[k] for k in (0, 1)]
+        if any(sides):
+            got = self.tr.exchange_records(out, s.mb, sides)
+            for r in got:
+                s.migrate_in(r)
+            if any(len(r) for r in got):
+                s.install_ghosts()
 
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
             self._exchange_halos()
-            n_div, n_leave = self.shard.step_local()
+            n_div, _ = self.shard.step_local()
             self.iteration += 1
-            st = self.tr.allgather([n_div, n_leave, self.shard.max_extent()])
-            self.emax_global = float(st[:, 2].max())
+            if not self.can_divide:
+                continue  # identifiers need the divisions of all slabs: one small all_gather per step
+            st = self.tr.allgather([n_div])
             if st[:, 0].sum() > 0:
                 gs, vx = self.shard.pending_divisions()
                 res = self.coord.divisions(self.tr.gather_divisions(gs, vx, st[:, 0].astype(np.int64)))
                 self.shard.apply_divisions(*res[self.rank])
-            if st[:, 1].sum() > 0:
-                self._migrate()
 
     def run(self):
         """Steps to t_max; returns the merged snapshots on every rank."""

@@ -222,6 +222,17 @@ int crm_sim_halo_pack(crm_sim* sim, int side, float width, void* dev_buf, uint32
  * max_extent = the largest extent among them (as reported by their owners). */
 int crm_sim_set_ghosts(crm_sim* sim, const void* dev_lo, uint32_t n_lo, const void* dev_hi, uint32_t n_hi,
                        float max_extent);
+/* The same per step with less host traffic: both messages [64-byte header {n_records, max_extent,
+ * flags} | records] packed in one call (NULL = no neighbour on that side) ... */
+int crm_sim_halo_pack_msgs(crm_sim* sim, float width, void* dev_msg_lo, void* dev_msg_hi, uint32_t cap,
+                           uint32_t flags, uint32_t* n_lo, uint32_t* n_hi);
+/* ... halo records of the owned rods that are about to migrate (centroid outside the slab): the
+ * old owner keeps them as ghosts during the hand-over step ... */
+int crm_sim_pack_leavers(crm_sim* sim, void* dev_buf, uint32_t cap, uint32_t* n);
+/* ... and the ghosts installed from the two received messages plus those leavers; returns the
+ * neighbours' record counts [2], flags [2] and the largest extent they reported. */
+int crm_sim_set_ghosts_msgs(crm_sim* sim, const void* dev_msg_lo, const void* dev_msg_hi, const void* dev_self,
+                            uint32_t n_self, uint32_t* counts, uint32_t* flags, float* max_extent);
 /* Migration (the reference re-sorts agents into voxels / sub-domains after every step): remove the
  * owned rods whose centroid left the slab and write their full records (device state, parameters,
  * identifier, parent, global slot) into HOST buffers; append received records as owned rods. */
