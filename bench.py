@@ -212,6 +212,7 @@ def main():
         clocks = sampler.stop()
         launches = sim.launch_count() - launches0
         tm = sim.read_timers()
+        lists = sim.list_stats()
         sim.enable_timers(False)
         sim.close()
 
@@ -274,6 +275,7 @@ def main():
         clocks = sampler.stop()
         launches = ds.shard.sim.launch_count() - launches0
         tm = ds.shard.sim.read_timers()
+        lists = ds.shard.sim.list_stats()
         ds.close()
 
         # e2e: host buffers in, K sharded steps, host buffers out
@@ -322,6 +324,7 @@ def main():
                 "d2h_bytes_per_step": d2h / K, "seconds": e2e_s},
         "gpu_launches": int(launches),
         "halo": halo,
+        "neighbour_lists": lists,
         "clocks": clocks,
         "roofline": {"kernel": "k_force<8>", "bound": "fp32", "achieved": achieved, "peak": fp32.value,
                      "unit": "TFLOP/s", "frac": achieved / fp32.value if fp32.value else None,

@@ -152,6 +152,8 @@ class Library:
             "sim_timer_start": (C.c_int, [vp]),
             "sim_timer_stop": (C.c_int, [vp, P(C.c_double)]),
             "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
+            "sim_set_skin": (C.c_int, [vp, C.c_float]),
+            "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),
             "sim_read_timers": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u64)]),
@@ -269,6 +271,14 @@ class Sim:
 
     def set_exact_math(self, exact: bool):
         self.L.check(self.L.fn("sim_set_exact_math")(self.h, int(exact)))
+
+    def set_skin(self, skin: float):
+        self.L.check(self.L.fn("sim_set_skin")(self.h, float(skin)))
+
+    def list_stats(self):
+        b, e = C.c_uint64(0), C.c_uint64(0)
+        self.L.check(self.L.fn("sim_list_stats")(self.h, C.byref(b), C.byref(e)))
+        return {"builds": int(b.value), "eval_steps": int(e.value)}
 
     def compute_forces(self):
         n, nv = self.n_rods, self.n_vertices

@@ -325,6 +325,12 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
                 d.status->err_slot = a;
         }
     }
+    if (d.vbuild) {  // displacement since the persistent neighbour structure was built
+        const float4 vb = d.vbuild[(size_t)a * LP + li];
+        const float ex = Pnew[0] - vb.x, ey = Pnew[1] - vb.y, ez = Pnew[2] - vb.z;
+        const float dd = group_max<LP>(hv ? ex * ex + ey * ey + ez * ez : 0.0f, gm);
+        if (l == 0) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
+    }
     float cx;
     const float ext = store_bounds<NV>(d, a, Pnew[0], Pnew[1], Pnew[2], l, gm, &cx);
     if (l == 0 && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);

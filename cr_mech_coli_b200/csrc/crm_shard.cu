@@ -180,6 +180,7 @@ extern "C" {
 int crm_sim_set_slab(crm_sim* s, float x_lo, float x_hi) {
     if (!s) return crm_fail(CRM_ERR_INVALID, "null sim");
     if (!(x_lo < x_hi)) return crm_fail(CRM_ERR_INVALID, "empty slab [%g, %g)", x_lo, x_hi);
+    if (s->n) return crm_fail(CRM_ERR_INVALID, "declare the slab before setting the agents");
     s->slab_lo = s->d.slab_lo = x_lo;
     s->slab_hi = s->d.slab_hi = x_hi;
     s->sharded = true;

@@ -56,6 +56,13 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.bsphere, on, (size_t)cap);
     G(s->d.chord, 2 * on, (size_t)2 * cap);
     G(s->d.vrec, on * s->lp, (size_t)cap * s->lp);
+    G(s->d.plist, 0, (size_t)cap * PL_MAXP_MAX);
+    G(s->d.pqo, 0, (size_t)cap * PL_QP * s->lp);
+    G(s->d.pqe, 0, (size_t)cap * PL_QP * s->lp);
+    G(s->d.pqs, 0, (size_t)cap * PL_QS * s->lp);
+    G(s->d.pnq, 0, (size_t)cap * s->lp);
+    G(s->d.vbuild, 0, (size_t)cap * s->lp);
+    s->need_rebuild = true;  // the structure does not survive a reallocation
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
     G(s->d.sorted, 0, (size_t)cap);
@@ -83,8 +90,12 @@ static int reserve_cells(crm_sim* s, uint32_t ncells) {
 
 // Centroid cell list geometry: the 3x3 stencil is complete when the cell edge is at
 // least 2*max_extent + search radius.
+// interaction range used by the search: inflated by the skin while the persistent structure is in use
+static bool persistent(const crm_sim* s) { return s->skin > 0.0f && !s->sharded; }
+static float search_radius(const crm_sim* s) { return s->rsearch + (persistent(s) ? s->skin : 0.0f); }
+
 static int configure_grid(crm_sim* s) {
-    const float h = (2.0f * std::max(s->emax, s->n_ghost ? s->emax_ghost : 0.0f) + s->rsearch) * 1.0005f + 1e-4f;
+    const float h = (2.0f * std::max(s->emax, s->n_ghost ? s->emax_ghost : 0.0f) + search_radius(s)) * 1.0005f + 1e-4f;
     double ncx = std::floor((double)s->cfg.domain_size[0] / h), ncy = std::floor((double)s->cfg.domain_size[1] / h);
     if (!(ncx >= 1.0)) ncx = 1.0;
     if (!(ncy >= 1.0)) ncy = 1.0;
@@ -243,16 +254,28 @@ static int handle_divisions(crm_sim* s, uint32_t n_div) {
     return crm_apply_divisions(s, idm.data(), idd.data(), gs.data());
 }
 
-static int launch_neighbour_and_force(crm_sim* s, bool count) {
+static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false) {
     int rc = configure_grid(s);
     if (rc) return rc;
     s->d.n = s->n + s->n_ghost;
     s->d.n_own = s->n;
-    s->d.rsearch = s->rsearch;
+    s->d.rsearch = search_radius(s);
+    s->d.skin = s->skin;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     s->launches += launch_binning(s->d, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
-    launch_force(s->nv, s->d, s->fast_math, count, s->stream);
+    launch_force(s->nv, s->d, s->fast_math, count, build, s->stream);
+    if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
+    s->launches += 1;
+    return 0;
+}
+
+// force of a step between two rebuilds: no cell list, no search (k_force_eval)
+static int launch_force_from_lists(crm_sim* s) {
+    s->d.n = s->d.n_own = s->n;
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
+    launch_force_eval(s->nv, s->d, s->fast_math, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
     s->launches += 1;
     return 0;
@@ -267,8 +290,25 @@ static int step_once(crm_sim* s) {
     s->iteration += 1;
     s->rod_steps += s->n;
     s->d.iteration = s->iteration;
-    int rc = launch_neighbour_and_force(s, false);
+    int rc;
+    const bool use_lists = persistent(s) && !s->need_rebuild;
+    if (use_lists) {
+        rc = launch_force_from_lists(s);
+        s->n_eval_steps += 1;
+    } else {
+        const bool build = persistent(s) && s->holdoff == 0;
+        rc = launch_neighbour_and_force(s, false, build);
+        if (build) {
+            if (s->steps_since_build < 3 && s->n_builds > 0) s->holdoff = 8;  // lists do not last: stop writing them for a while
+            s->n_builds += 1;
+            s->steps_since_build = 0;
+            s->need_rebuild = false;
+        } else if (s->holdoff) {
+            s->holdoff -= 1;
+        }
+    }
     if (rc) return rc;
+    s->steps_since_build += 1;
     launch_integrate(s->nv, s->d, s->stream);
     s->launches += 1;
     CK(cudaGetLastError());
@@ -281,7 +321,16 @@ static int step_once(crm_sim* s) {
     }
     if ((rc = crm_report_device_error(s))) return rc;
     s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);  // owned rods; ghosts are re-sent before the next step
+    if (persistent(s)) {
+        if (s->h_status->plist_overflow) {  // a rod did not fit: search every step for a while, then retry
+            s->need_rebuild = true;
+            s->holdoff = 64;
+        }
+        const float disp = std::sqrt(__builtin_bit_cast(float, s->h_status->disp2_bits));
+        if (!(disp < 0.4999f * s->skin)) s->need_rebuild = true;
+    }
     const uint32_t n_div = s->h_status->n_div;
+    if (n_div) s->need_rebuild = true;
     if (n_div) {
         if (s->sharded) {  // identifiers need the divisions of all slabs: crm_sim_apply_divisions
             if ((rc = fetch_divisions(s, n_div))) return rc;
@@ -389,6 +438,7 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     s->vox_counter.assign((size_t)c->n_voxels[0] * c->n_voxels[1], 0);
     const char* ex = getenv("CRM_B200_EXACT_MATH");
     s->fast_math = !(ex && ex[0] == '1');
+    if (const char* sk = getenv("CRM_B200_SKIN")) s->skin = std::max(0.0f, (float)atof(sk));
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaMalloc(&s->d.status, sizeof(Status)));
     CK(cudaMemset(s->d.status, 0, sizeof(Status)));
@@ -417,7 +467,7 @@ void crm_sim_destroy(crm_sim* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
-                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.cell_of, s->d.cell_rank,
+                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.cell_of, s->d.cell_rank,
                     s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -428,6 +478,20 @@ void crm_sim_destroy(crm_sim* s) {
     if (s->ev_t1) cudaEventDestroy(s->ev_t1);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
+}
+
+int crm_sim_set_skin(crm_sim* s, float skin) {
+    if (!s || !(skin >= 0.0f)) return fail(CRM_ERR_INVALID, "skin must be >= 0");
+    if (s->n) return fail(CRM_ERR_INVALID, "set the skin before the agents");
+    s->skin = skin;
+    s->need_rebuild = true;
+    return 0;
+}
+
+int crm_sim_list_stats(const crm_sim* s, uint64_t* n_builds, uint64_t* n_eval_steps) {
+    if (n_builds) *n_builds = s->n_builds;
+    if (n_eval_steps) *n_eval_steps = s->n_eval_steps;
+    return 0;
 }
 
 int crm_sim_set_exact_math(crm_sim* s, int exact) {
@@ -473,7 +537,11 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         cmax = std::max(cmax, par[a].cutoff);
     }
     s->rsearch = std::max(cmax, 2.0f * rmax * 0.70710678f) * 1.0001f;
-    s->d.rsearch = s->rsearch;  // the bounds kernels bake it into the cull thresholds
+    s->d.rsearch = search_radius(s);  // the bounds kernels bake it into the cull thresholds
+    s->d.skin = s->skin;
+    s->need_rebuild = true;
+    s->holdoff = 0;
+    s->steps_since_build = 0;
     const size_t m = (size_t)n * nv * 3;
     if (n) {
         CK(cudaMemcpyAsync(s->stage, pos, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
@@ -575,6 +643,7 @@ int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
     if (s->n == 0) return 0;
     int rc = launch_neighbour_and_force(s, true);
     if (rc) return rc;
+    s->need_rebuild = true;  // the cell order the persistent structure is indexed by has been rewritten
     CK(cudaGetLastError());
     if ((rc = crm_read_status(s))) return rc;
     s->last_pairs_cut = s->h_status->pairs_in_cutoff;

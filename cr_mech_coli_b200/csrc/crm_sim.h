@@ -20,7 +20,8 @@ void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_
 void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
 void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
 int launch_binning(const Dev& d, cudaStream_t st);
-void launch_force(int nv, const Dev& d, bool fast, bool count, cudaStream_t st);
+void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
+void launch_force_eval(int nv, const Dev& d, bool fast, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
 void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st);
 // host helpers (crm_host.cpp)
@@ -62,6 +63,12 @@ struct crm_sim {
     float emax_ghost = 0.0f;  // ... over the current ghost rods
     float rsearch = 0.0f;
     bool fast_math = true;
+    // persistent neighbour structure (Verlet lists): valid until a vertex moved more than skin/2
+    float skin = 0.5f;          // um; 0 disables the structure (every step searches from scratch)
+    bool need_rebuild = true;   // the next step must search (and rebuild the structure)
+    uint32_t holdoff = 0;       // steps for which rebuilding is not attempted (overflow / frequent rebuilds)
+    uint32_t steps_since_build = 0;
+    uint64_t n_builds = 0, n_eval_steps = 0;
     // host-side bookkeeping
     std::vector<crm_rod_params> base;  // cold fields per slot
     std::vector<crm_ident> ids, parents;

@@ -170,6 +170,14 @@ int crm_sim_compute_forces(crm_sim* sim, float* out_force, uint32_t* out_n_neigh
  * approximations (rsqrt/ex2/lg2/rcp).  Env CRM_B200_EXACT_MATH=1 sets the default. */
 int crm_sim_set_exact_math(crm_sim* sim, int exact);
 
+/* Skin (um) of the persistent neighbour structure: rods and point-segment evaluations within
+ * range + skin are listed once and reused until a vertex has moved more than skin/2 (Verlet
+ * lists; results are identical because skipped evaluations are exact zeros).  0 = search from
+ * scratch every step.  Default 0.5 or env CRM_B200_SKIN.  Must precede crm_sim_set_agents. */
+int crm_sim_set_skin(crm_sim* sim, float skin);
+/* Steps that rebuilt the structure / steps that reused it. */
+int crm_sim_list_stats(const crm_sim* sim, uint64_t* n_builds, uint64_t* n_eval_steps);
+
 uint32_t crm_sim_n_rods(const crm_sim* sim);
 uint32_t crm_sim_n_vertices(const crm_sim* sim);
 uint64_t crm_sim_iteration(const crm_sim* sim);

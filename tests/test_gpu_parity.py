@@ -148,3 +148,75 @@ def test_boundary_error(product_lib):
     g.set_agents(pos, vel, par)
     with pytest.raises(_capi.SimulationError, match="BoundaryError"):
         g.step(3)
+
+
+def test_persistent_lists_match_search_every_step(product_lib):
+    """The persistent neighbour structure (Verlet lists with a skin) skips only exact zeros: stepping
+    with it equals stepping with a fresh search every step, and equals the oracle."""
+    n = 1500
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.05)
+    pos = lattice_colony(n, seed=9)
+    par = mie_params(n, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    vel = np.random.default_rng(3).normal(0, 0.3, pos.shape).astype(np.float32)  # enough motion to force rebuilds
+    vel[:, :, 2] = 0
+    steps = 120
+    out = {}
+    for skin in (0.0, 0.5, 0.1):
+        g = _capi.Sim(product_lib, cfg)
+        g.set_skin(skin)
+        g.set_agents(pos, vel, par)
+        g.step(steps)
+        out[skin] = (g.get_state(), g.list_stats())
+        g.close()
+    o = oracle.sim(cfg)
+    o.set_agents(pos, vel, par)
+    o.step(steps)
+    po, vo = o.get_state()[:2]
+    assert out[0.0][1] == {"builds": 0, "eval_steps": 0}
+    assert out[0.5][1]["eval_steps"] > steps // 2 and out[0.5][1]["builds"] >= 2
+    assert out[0.1][1]["builds"] > out[0.5][1]["builds"]
+    for skin in (0.0, 0.5, 0.1):
+        (pg, vg, parg, _, _), _ = out[skin]
+        assert np.abs(pg - po).max() < TRAJ_ATOL, (skin, np.abs(pg - po).max())
+        assert (parg["n_neighbors"] == o.get_state()[2]["n_neighbors"]).all()
+    assert np.abs(out[0.5][0][0] - out[0.0][0][0]).max() < 2e-5
+
+
+def test_persistent_lists_neighbor_sensing_dense(product_lib):
+    """Neighbour counts from the sensing candidates of the persistent structure (dense, overlapping
+    rods: many vertex pairs inside the sensing radius) equal the oracle's at every step."""
+    n, L = 110, 220.0
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(1, 1), dt=0.02)
+    pos = random_colony(n, L, seed=8, z_spread=0.3)
+    par = morse_params(n, radius=1.5, cutoff=5.0, strength=0.02, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    g, o = _pair(cfg, pos, par, product_lib)
+    for _ in range(6):
+        g.step(5)
+        o.step(5)
+        pg, _, parg, _, _ = g.get_state()
+        po, _, paro, _, _ = o.get_state()
+        assert np.abs(pg - po).max() < TRAJ_ATOL
+        assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
+    assert g.list_stats()["eval_steps"] > 0
+    assert paro["n_neighbors"].max() >= 2  # the case does exercise the sensing radius
+
+
+def test_persistent_lists_overflow_falls_back(product_lib):
+    """A colony too dense for the fixed-capacity structure (> 16 neighbour rods) silently keeps
+    searching every step; results still match the oracle."""
+    n, L = 400, 120.0
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(1, 1), dt=0.02)
+    pos = random_colony(n, L, seed=8, z_spread=0.3)
+    par = morse_params(n, radius=1.5, cutoff=5.0, strength=0.02, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    g, o = _pair(cfg, pos, par, product_lib)
+    g.step(12)
+    o.step(12)
+    pg, _, parg, _, _ = g.get_state()
+    po, _, paro, _, _ = o.get_state()
+    assert np.abs(pg - po).max() < TRAJ_ATOL
+    assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
+    assert g.list_stats()["eval_steps"] == 0
