@@ -167,7 +167,10 @@ class Library:
             "sim_search_radius": (C.c_float, [vp]),
             "sim_halo_pack": (C.c_int, [vp, C.c_int, C.c_float, vp, u32, P(u32)]),
             "sim_set_ghosts": (C.c_int, [vp, vp, u32, vp, u32, C.c_float]),
-            "sim_halo_pack_msgs": (C.c_int, [vp, C.c_float, vp, vp, u32, u32, P(u32), P(u32)]),
+            "sim_halo_pack_msgs": (C.c_int, [vp, C.c_float, vp, vp, u32, u32, C.c_int, P(u32), P(u32)]),
+            "sim_wants_rebuild": (C.c_int, [vp]),
+            "sim_keep_lists": (C.c_int, [vp]),
+            "sim_skin": (C.c_float, [vp]),
             "sim_pack_leavers": (C.c_int, [vp, vp, u32, P(u32)]),
             "sim_set_ghosts_msgs": (C.c_int, [vp, vp, vp, vp, u32, vp, vp, P(C.c_float)]),
             "sim_migrate_out": (C.c_int, [vp, vp, u32, P(u32), vp, u32, P(u32)]),

@@ -201,7 +201,14 @@ uint32_t crm_sim_migrant_record_bytes(const crm_sim* s) {
     return (uint32_t)state_words(s->lp) * 4u + (uint32_t)sizeof(HostTail);
 }
 float crm_sim_max_extent(const crm_sim* s) { return s->emax; }
-float crm_sim_search_radius(const crm_sim* s) { return s->rsearch; }
+float crm_sim_search_radius(const crm_sim* s) { return s->rsearch + (s->skin > 0.0f ? s->skin : 0.0f); }
+float crm_sim_skin(const crm_sim* s) { return s->skin; }
+int crm_sim_wants_rebuild(const crm_sim* s) { return s->want_rebuild ? 1 : 0; }
+// All slabs agreed that nothing moved far enough: the next step reuses the persistent structure.
+int crm_sim_keep_lists(crm_sim* s) {
+    if (s->have_lists && !s->want_rebuild) s->need_rebuild = false;
+    return s->need_rebuild ? 0 : 1;
+}
 
 int crm_sim_halo_pack(crm_sim* s, int side, float width, void* dev_buf, uint32_t cap, uint32_t* n_out) {
     if (!s || !n_out) return crm_fail(CRM_ERR_INVALID, "null argument");
@@ -250,33 +257,45 @@ int crm_sim_set_ghosts(crm_sim* s, const void* dev_lo, uint32_t n_lo, const void
 // Both halo messages of a step in one call: [64-byte header {n, max_extent, flags} | records].
 // One stream synchronisation; the counts come back for the caller's bookkeeping.
 int crm_sim_halo_pack_msgs(crm_sim* s, float width, void* dev_msg_lo, void* dev_msg_hi, uint32_t cap,
-                           uint32_t flags, uint32_t* n_lo, uint32_t* n_hi) {
+                           uint32_t flags, int reselect, uint32_t* n_lo, uint32_t* n_hi) {
     if (!s) return crm_fail(CRM_ERR_INVALID, "null argument");
     CK(cudaSetDevice(s->device));
-    uint32_t n[2] = {0, 0};
     void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    if (s->halo_sel_cap < cap) {
+        for (int side = 0; side < 2; ++side) {
+            if (s->halo_sel[side]) CK(cudaFree(s->halo_sel[side]));
+            CK(cudaMalloc(&s->halo_sel[side], sizeof(uint32_t) * (cap + 1)));  // [count | slots]
+            s->halo_sel_n[side] = 0;
+        }
+        s->halo_sel_cap = cap;
+        reselect = 1;
+    }
     for (int side = 0; side < 2; ++side) {
         if (!msg[side]) continue;
-        const float lo = side == 0 ? -INFINITY : s->slab_hi - width;
-        const float hi = side == 0 ? s->slab_lo + width : INFINITY;
-        int rc = select_band(s, lo, hi, &n[side]);
-        if (rc) return rc;
-        if (n[side] > cap)
-            return crm_fail(CRM_ERR_NOMEM, "halo of %u rods exceeds the exchange buffer (%u records)", n[side], cap);
-        if (!s->select_count) CK(cudaMalloc(&s->select_count, sizeof(uint32_t)));
-        if (s->n == 0) CK(cudaMemsetAsync(s->select_count, 0, sizeof(uint32_t), s->stream));
-        k_write_header<<<1, 1, 0, s->stream>>>((uint32_t*)msg[side], s->select_count, s->emax, flags);
-        if (n[side]) {
-            const uint64_t threads = (uint64_t)n[side] * (s->lp + 5);
-            k_halo_gather<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
-                s->d, s->select_out, n[side], s->lp, reinterpret_cast<float4*>((char*)msg[side] + 64));
+        if (reselect) {  // otherwise the selection of the last rebuild stays frozen (ghost slots stay put)
+            uint32_t n = 0;
+            const float lo = side == 0 ? -INFINITY : s->slab_hi - width;
+            const float hi = side == 0 ? s->slab_lo + width : INFINITY;
+            int rc = select_band(s, lo, hi, &n);
+            if (rc) return rc;
+            if (n > cap) return crm_fail(CRM_ERR_NOMEM, "halo of %u rods exceeds the exchange buffer (%u records)", n, cap);
+            s->halo_sel_n[side] = n;
+            CK(cudaMemcpyAsync(s->halo_sel[side], &s->halo_sel_n[side], sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
+            if (n) CK(cudaMemcpyAsync(s->halo_sel[side] + 1, s->select_out, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, s->stream));
         }
-        s->launches += 3;
+        const uint32_t n = s->halo_sel_n[side];
+        k_write_header<<<1, 1, 0, s->stream>>>((uint32_t*)msg[side], s->halo_sel[side], s->emax, flags);
+        if (n) {
+            const uint64_t threads = (uint64_t)n * (s->lp + 5);
+            k_halo_gather<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
+                s->d, s->halo_sel[side] + 1, n, s->lp, reinterpret_cast<float4*>((char*)msg[side] + 64));
+        }
+        s->launches += 2 + (reselect ? 1 : 0);
     }
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(s->stream));  // the transport above the ABI runs on other streams
-    if (n_lo) *n_lo = n[0];
-    if (n_hi) *n_hi = n[1];
+    if (n_lo) *n_lo = s->halo_sel_n[0];
+    if (n_hi) *n_hi = s->halo_sel_n[1];
     return 0;
 }
 
@@ -431,6 +450,8 @@ int crm_sim_migrate_out(crm_sim* s, void* host_lo, uint32_t cap_lo, uint32_t* n_
     s->gslot.resize(n_new);
     s->n = n_new;
     s->n_ghost = 0;
+    s->need_rebuild = true;
+    s->have_lists = false;
     s->d.n = s->d.n_own = n_new;
     // bounds (vertex records, spheres, chords) of the moved slots
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
@@ -478,6 +499,8 @@ int crm_sim_migrate_in(crm_sim* s, const void* host_buf, uint32_t n_in) {
     CK(cudaGetLastError());
     s->n = n0 + n_in;
     s->n_ghost = 0;
+    s->need_rebuild = true;
+    s->have_lists = false;
     s->d.n = s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     launch_bounds_kernel(s->nv, s->d, s->stream);

@@ -63,6 +63,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.pnq, 0, (size_t)cap * s->lp);
     G(s->d.vbuild, 0, (size_t)cap * s->lp);
     s->need_rebuild = true;  // the structure does not survive a reallocation
+    s->have_lists = false;
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
     G(s->d.sorted, 0, (size_t)cap);
@@ -91,7 +92,7 @@ static int reserve_cells(crm_sim* s, uint32_t ncells) {
 // Centroid cell list geometry: the 3x3 stencil is complete when the cell edge is at
 // least 2*max_extent + search radius.
 // interaction range used by the search: inflated by the skin while the persistent structure is in use
-static bool persistent(const crm_sim* s) { return s->skin > 0.0f && !s->sharded; }
+static bool persistent(const crm_sim* s) { return s->skin > 0.0f; }
 static float search_radius(const crm_sim* s) { return s->rsearch + (persistent(s) ? s->skin : 0.0f); }
 
 static int configure_grid(crm_sim* s) {
@@ -231,6 +232,8 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     s->emax = std::max(s->emax, __builtin_bit_cast(float, s->h_status->emax_bits));
     s->h_div.clear();
     s->pending_div = 0;
+    s->need_rebuild = true;
+    s->have_lists = false;
     return 0;
 }
 
@@ -272,7 +275,8 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
 
 // force of a step between two rebuilds: no cell list, no search (k_force_eval)
 static int launch_force_from_lists(crm_sim* s) {
-    s->d.n = s->d.n_own = s->n;
+    s->d.n = s->n + s->n_ghost;  // the build order covers the ghosts as well
+    s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
     launch_force_eval(s->nv, s->d, s->fast_math, s->stream);
@@ -291,7 +295,7 @@ static int step_once(crm_sim* s) {
     s->rod_steps += s->n;
     s->d.iteration = s->iteration;
     int rc;
-    const bool use_lists = persistent(s) && !s->need_rebuild;
+    const bool use_lists = persistent(s) && !s->need_rebuild && s->have_lists;
     if (use_lists) {
         rc = launch_force_from_lists(s);
         s->n_eval_steps += 1;
@@ -299,12 +303,19 @@ static int step_once(crm_sim* s) {
         const bool build = persistent(s) && s->holdoff == 0;
         rc = launch_neighbour_and_force(s, false, build);
         if (build) {
-            if (s->steps_since_build < 3 && s->n_builds > 0) s->holdoff = 8;  // lists do not last: stop writing them for a while
+            // lists that repeatedly do not last (dividing colonies): stop writing them for a while
+            s->short_builds = (s->steps_since_build < 3 && s->n_builds > 0) ? s->short_builds + 1 : 0;
+            if (s->short_builds >= 4) {
+                s->holdoff = 8;
+                s->short_builds = 0;
+            }
             s->n_builds += 1;
             s->steps_since_build = 0;
             s->need_rebuild = false;
-        } else if (s->holdoff) {
-            s->holdoff -= 1;
+            s->have_lists = true;
+        } else {
+            s->have_lists = false;  // a plain search: whatever structure is on the device is stale
+            if (s->holdoff) s->holdoff -= 1;
         }
     }
     if (rc) return rc;
@@ -321,16 +332,19 @@ static int step_once(crm_sim* s) {
     }
     if ((rc = crm_report_device_error(s))) return rc;
     s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);  // owned rods; ghosts are re-sent before the next step
+    const uint32_t n_div = s->h_status->n_div;
+    bool want = n_div > 0 || s->h_status->n_leave > 0;
     if (persistent(s)) {
         if (s->h_status->plist_overflow) {  // a rod did not fit: search every step for a while, then retry
-            s->need_rebuild = true;
+            s->have_lists = false;
             s->holdoff = 64;
         }
         const float disp = std::sqrt(__builtin_bit_cast(float, s->h_status->disp2_bits));
-        if (!(disp < 0.4999f * s->skin)) s->need_rebuild = true;
+        if (!(disp < 0.4999f * s->skin)) want = true;
     }
-    const uint32_t n_div = s->h_status->n_div;
-    if (n_div) s->need_rebuild = true;
+    s->want_rebuild = want || !s->have_lists;
+    // sharded runs rebuild in all slabs at once: the coordinator clears the flag (crm_sim_keep_lists)
+    if (s->sharded || s->want_rebuild) s->need_rebuild = true;
     if (n_div) {
         if (s->sharded) {  // identifiers need the divisions of all slabs: crm_sim_apply_divisions
             if ((rc = fetch_divisions(s, n_div))) return rc;
@@ -468,7 +482,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -540,6 +554,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->d.rsearch = search_radius(s);  // the bounds kernels bake it into the cull thresholds
     s->d.skin = s->skin;
     s->need_rebuild = true;
+    s->have_lists = false;
     s->holdoff = 0;
     s->steps_since_build = 0;
     const size_t m = (size_t)n * nv * 3;
@@ -644,6 +659,7 @@ int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
     int rc = launch_neighbour_and_force(s, true);
     if (rc) return rc;
     s->need_rebuild = true;  // the cell order the persistent structure is indexed by has been rewritten
+    s->have_lists = false;
     CK(cudaGetLastError());
     if ((rc = crm_read_status(s))) return rc;
     s->last_pairs_cut = s->h_status->pairs_in_cutoff;

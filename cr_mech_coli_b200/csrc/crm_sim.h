@@ -66,8 +66,15 @@ struct crm_sim {
     // persistent neighbour structure (Verlet lists): valid until a vertex moved more than skin/2
     float skin = 0.5f;          // um; 0 disables the structure (every step searches from scratch)
     bool need_rebuild = true;   // the next step must search (and rebuild the structure)
+    bool have_lists = false;    // the structure on the device describes the current slots
+    bool want_rebuild = true;   // outcome of the last step: a local reason to rebuild (sharded runs: the
+                                // coordinator combines the slabs' wishes, crm_sim_keep_lists)
+    uint32_t* halo_sel[2] = {nullptr, nullptr};  // frozen halo selections (slots) per side
+    uint32_t halo_sel_n[2] = {0, 0};
+    uint32_t halo_sel_cap = 0;
     uint32_t holdoff = 0;       // steps for which rebuilding is not attempted (overflow / frequent rebuilds)
     uint32_t steps_since_build = 0;
+    uint32_t short_builds = 0;  // consecutive rebuilds that lasted fewer than 3 steps
     uint64_t n_builds = 0, n_eval_steps = 0;
     // host-side bookkeeping
     std::vector<crm_rod_params> base;  // cold fields per slot

@@ -186,17 +186,26 @@ class Shard:
 
     def halo_width(self, emax_global: float) -> float:
         """A rod interacts with rods whose centroid is at most ext_a + ext_b + range away."""
-        r = float(self.lib.fn("sim_search_radius")(self.sim.h))
-        return (self.max_extent() + emax_global) * 1.02 + r * 1.02 + 1e-3
+        r = float(self.lib.fn("sim_search_radius")(self.sim.h))  # includes the skin of the persistent lists
+        skin = float(self.lib.fn("sim_skin")(self.sim.h))  # frozen halos: rods may drift skin/2 each before a rebuild
+        return (self.max_extent() + emax_global) * 1.02 + r * 1.02 + skin + 1e-3
 
     # -- halo ----------------------------------------------------------------
-    def begin_step(self, emax_nb: float):
-        """Hand over the rods that left the slab during the last step (their halo records stay here
-        as ghosts for this step), then pack both halo messages.  Returns the migrant records
-        (host bytes) for the lower / upper neighbour."""
+    def begin_step(self, emax_nb: float, rebuild: bool = True):
+        """Pack both halo messages.  On a rebuild step the rods that left the slab are handed over
+        first (their halo records stay here as ghosts for this step) and the halo bands are
+        selected afresh; otherwise the frozen selection of the last rebuild is re-sent and the
+        persistent neighbour structure is kept.  Returns the migrant records (host bytes) for the
+        lower / upper neighbour."""
         L, h = self.lib, self.sim.h
         out = (np.zeros(0, np.uint8), np.zeros(0, np.uint8))
         self.n_self = 0
+        if not rebuild:
+            L.check(L.fn("sim_halo_pack_msgs")(h, 0.0, C.c_void_p(self.send[0].data_ptr()) if self.rank > 0 else None,
+                                               C.c_void_p(self.send[1].data_ptr()) if self.rank + 1 < self.partition.world else None,
+                                               self.halo_cap, 0, 0, None, None))
+            L.fn("sim_keep_lists")(h)
+            return out
         if self.n_leave:
             n = C.c_uint32(0)
             L.check(L.fn("sim_pack_leavers")(h, C.c_void_p(self.selfbuf.data_ptr()), self.halo_cap, C.byref(n)))
@@ -207,7 +216,7 @@ class Shard:
         width = self.halo_width(max(emax_nb, self.max_extent()))
         lo = C.c_void_p(self.send[0].data_ptr()) if self.rank > 0 else None
         hi = C.c_void_p(self.send[1].data_ptr()) if self.rank + 1 < self.partition.world else None
-        L.check(L.fn("sim_halo_pack_msgs")(h, width, lo, hi, self.halo_cap, flags, None, None))
+        L.check(L.fn("sim_halo_pack_msgs")(h, width, lo, hi, self.halo_cap, flags, 1, None, None))
         return out
 
     def install_ghosts(self):
@@ -227,10 +236,11 @@ class Shard:
 
     # -- step ----------------------------------------------------------------
     def step_local(self):
+        """One local step; returns (pending divisions, 1 if this slab has a reason to rebuild)."""
         self.sim.step(1)
         n_div = int(self.lib.fn("sim_pending_divisions")(self.sim.h, None, None, 0))
         self.n_leave = int(self.lib.fn("sim_n_leaving")(self.sim.h))
-        return n_div, self.n_leave
+        return n_div, int(self.lib.fn("sim_wants_rebuild")(self.sim.h))
 
     def pending_divisions(self):
         L, h = self.lib, self.sim.h
@@ -329,10 +339,14 @@ class LocalCluster:
             s.set_agents(*part)
         self.coord = _Coordinator(self.cfg, len(pos))
         self.emax_nb = [max(s.max_extent() for s in self.shards)] * len(self.shards)
+        self.rebuild_next = True
 
     def _exchange_halos(self):
         w = len(self.shards)
-        outs = [s.begin_step(self.emax_nb[r]) for r, s in enumerate(self.shards)]
+        rebuild = self.rebuild_next
+        outs = [s.begin_step(self.emax_nb[r], rebuild) for r, s in enumerate(self.shards)]
+        # ownership changed hands: the hand-over ghosts exist for this step only, rebuild again next step
+        self.moved = any(len(o[0]) or len(o[1]) for o in outs)
         for r, s in enumerate(self.shards):
             if r > 0:
                 s.recv[0].copy_(self.shards[r - 1].send[1])
@@ -359,6 +373,7 @@ class LocalCluster:
             self._exchange_halos()
             status = [s.step_local() for s in self.shards]
             self.iteration += 1
+            self.rebuild_next = any(w for _, w in status) or self.moved  # rebuilds are collective
             if any(nd for nd, _ in status):
                 res = self.coord.divisions([s.pending_divisions() for s in self.shards])
                 for s, r in zip(self.shards, res):
@@ -366,6 +381,7 @@ class LocalCluster:
 
     def compute_forces(self):
         """Forces / neighbour counts of the current state in global-slot order."""
+        self.rebuild_next = True
         self._exchange_halos()
         parts = [s.sim.compute_forces() + (s.global_slots(),) for s in self.shards]
         gs = np.concatenate([p[2] for p in parts])
@@ -482,6 +498,8 @@ class DistributedShard:
         st = self.tr.allgather([self.shard.max_extent(), float(self.shard.can_divide)])
         self.emax_global = float(st[:, 0].max())
         self.can_divide = bool(st[:, 1].max() > 0)
+        self.use_lists = float(self.shard.lib.fn("sim_skin")(self.shard.sim.h)) > 0.0
+        self.rebuild_next = True
         need = 2.0 * self.shard.halo_width(self.emax_global)
         if self.partition.min_width() < need:
             raise ValueError(f"slabs narrower than two halo widths ({need:.1f} um): use fewer GPUs")
@@ -492,13 +510,14 @@ class DistributedShard:
 
     def _exchange_halos(self):
         s = self.shard
-        out = s.begin_step(self.emax_global)
+        out = s.begin_step(self.emax_global, self.rebuild_next)
         self.tr.sendrecv(s.send, s.recv)
         counts, incoming, emax = s.install_ghosts()
         self.last_counts = counts
         self.emax_global = max(emax, s.max_extent())
         # migrants travel only between neighbours that announced them in the message headers
         sides = [bool(len(out[k])) or incoming[k] for k in (0, 1)]
+        self.moved = any(sides)  # the hand-over ghosts exist for this step only: rebuild again next step
         if any(sides):
             got = self.tr.exchange_records(out, s.mb, sides)
             for r in got:
@@ -509,11 +528,14 @@ class DistributedShard:
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
             self._exchange_halos()
-            n_div, _ = self.shard.step_local()
+            n_div, want = self.shard.step_local()
             self.iteration += 1
-            if not self.can_divide:
-                continue  # identifiers need the divisions of all slabs: one small all_gather per step
-            st = self.tr.allgather([n_div])
+            if not (self.can_divide or self.use_lists):
+                continue  # nothing to agree on: every step searches afresh
+            # one small all_gather per step: divisions need the lists of all slabs for the identifiers,
+            # and the persistent neighbour structure is rebuilt in all slabs at once
+            st = self.tr.allgather([n_div, int(want or self.moved)])
+            self.rebuild_next = bool(st[:, 1].max() > 0) or not self.use_lists
             if st[:, 0].sum() > 0:
                 gs, vx = self.shard.pending_divisions()
                 res = self.coord.divisions(self.tr.gather_divisions(gs, vx, st[:, 0].astype(np.int64)))

@@ -233,7 +233,15 @@ int crm_sim_set_ghosts(crm_sim* sim, const void* dev_lo, uint32_t n_lo, const vo
 /* The same per step with less host traffic: both messages [64-byte header {n_records, max_extent,
  * flags} | records] packed in one call (NULL = no neighbour on that side) ... */
 int crm_sim_halo_pack_msgs(crm_sim* sim, float width, void* dev_msg_lo, void* dev_msg_hi, uint32_t cap,
-                           uint32_t flags, uint32_t* n_lo, uint32_t* n_hi);
+                           uint32_t flags, int reselect, uint32_t* n_lo, uint32_t* n_hi);
+/* reselect = 0 re-sends the rods chosen at the last reselect (frozen halo: ghost slots stay put, which
+ * is what lets the receiver keep its persistent neighbour structure between rebuilds).
+ * Rebuilds are collective: after a step every slab reports crm_sim_wants_rebuild; if none does, the
+ * coordinator calls crm_sim_keep_lists on all of them, otherwise the next step reselects the halos
+ * and searches again everywhere. */
+int crm_sim_wants_rebuild(const crm_sim* sim);
+int crm_sim_keep_lists(crm_sim* sim);
+float crm_sim_skin(const crm_sim* sim);
 /* ... halo records of the owned rods that are about to migrate (centroid outside the slab): the
  * old owner keeps them as ghosts during the hand-over step ... */
 int crm_sim_pack_leavers(crm_sim* sim, void* dev_buf, uint32_t cap, uint32_t* n);

@@ -142,3 +142,38 @@ def test_two_process_nccl(product_lib):
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "dist_worker ok" in r.stdout
+
+
+def test_sharded_persistent_lists(product_lib):
+    """Collective rebuilds with frozen halos: the slabs reuse their persistent neighbour structure
+    between rebuilds (most steps) and still follow the unsharded trajectory; rods that drift over
+    the slab edges force rebuilds and change owner."""
+    n = 1500
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(1, 1), dt=0.01)
+    pos = lattice_colony(n, seed=6)
+    par = mie_params(n, growth_rate=0.0, damping=0.0)
+    par["spring_length_threshold"] = 1e30
+    vel = np.zeros_like(pos)
+    vel[:, :, 0] = 1.0  # 0.01 um per step: a rebuild every ~25 steps, a few rods change owner
+    # lattice columns sit at x = 14 + 24 k (+- 0.25 jitter): columns 5 and 10 cross these edges
+    # between steps ~150 and ~200; outside that window nothing changes owner
+    part = sharded.SlabPartition([14 + 5 * 24 + 1.75, 14 + 10 * 24 + 1.75])
+    cl = sharded.LocalCluster(product_lib, cfg, part)
+    cl.set_agents(pos, vel, par)
+    n0 = [s.n_rods for s in cl.shards]
+    steps = 400
+    cl.step(steps)
+    stats = [s.sim.list_stats() for s in cl.shards]
+    assert all(st["eval_steps"] > steps // 2 for st in stats), stats
+    assert all(3 <= st["builds"] < steps // 4 for st in stats), stats
+    n1 = [s.n_rods for s in cl.shards]
+    assert sum(n1) == n and n1 != n0
+    ps, vs, pars, ids, parents = cl.get_state()
+    with _capi.Sim(product_lib, cfg) as g:
+        g.set_agents(pos, vel, par)
+        g.step(steps)
+        pg, vg, parg, idg, prg = g.get_state()
+    assert (ids == idg).all()
+    assert np.abs(ps - pg).max() < 1e-3
+    cl.close()
