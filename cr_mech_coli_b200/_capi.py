@@ -164,6 +164,7 @@ class Library:
             "sim_halo_record_bytes": (u32, [vp]),
             "sim_migrant_record_bytes": (u32, [vp]),
             "sim_max_extent": (C.c_float, [vp]),
+            "sim_refresh_bounds": (C.c_int, [vp]),
             "sim_search_radius": (C.c_float, [vp]),
             "sim_halo_pack": (C.c_int, [vp, C.c_int, C.c_float, vp, u32, P(u32)]),
             "sim_set_ghosts": (C.c_int, [vp, vp, u32, vp, u32, C.c_float]),

@@ -331,9 +331,13 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         const float dd = group_max<LP>(hv ? ex * ex + ey * ey + ez * ez : 0.0f, gm);
         if (l == 0) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
     }
-    float cx;
-    const float ext = store_bounds<NV>(d, a, Pnew[0], Pnew[1], Pnew[2], l, gm, &cx);
-    if (l == 0 && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);
+    // The bounds of the search (sphere, chord, cull thresholds) are recomputed by k_bounds only when a
+    // search follows (rebuild steps); every step needs just the vertex record of the force kernel.
+    d.vrec[(size_t)a * LP + l] = make_float4(Pnew[0], Pnew[1], Pnew[2], -1.0f);
+    if (d.slab_lo > -INFINITY || d.slab_hi < INFINITY) {  // sharded: rods whose centroid left the slab
+        const float cx = group_sum<LP>(hv ? Pnew[0] : 0.0f, gm) * (1.0f / NV);
+        if (l == 0 && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);
+    }
     if (dividing) {
         // user voxel of the mother = voxel of the mean vertex at the start of the step,
         // summed sequentially like the reference (nalgebra row_mean)
@@ -362,7 +366,6 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         gs.z = newL;
         d.grow[a] = gs;
         if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
-        atomicMax(&d.status->emax_bits, __float_as_uint(ext));
     }
 }
 

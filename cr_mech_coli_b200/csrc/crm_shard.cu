@@ -201,6 +201,11 @@ uint32_t crm_sim_migrant_record_bytes(const crm_sim* s) {
     return (uint32_t)state_words(s->lp) * 4u + (uint32_t)sizeof(HostTail);
 }
 float crm_sim_max_extent(const crm_sim* s) { return s->emax; }
+int crm_sim_refresh_bounds(crm_sim* s) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null sim");
+    CK(cudaSetDevice(s->device));
+    return crm_refresh_bounds(s);
+}
 float crm_sim_search_radius(const crm_sim* s) { return s->rsearch + (s->skin > 0.0f ? s->skin : 0.0f); }
 float crm_sim_skin(const crm_sim* s) { return s->skin; }
 int crm_sim_wants_rebuild(const crm_sim* s) { return s->want_rebuild ? 1 : 0; }
@@ -213,6 +218,10 @@ int crm_sim_keep_lists(crm_sim* s) {
 int crm_sim_halo_pack(crm_sim* s, int side, float width, void* dev_buf, uint32_t cap, uint32_t* n_out) {
     if (!s || !n_out) return crm_fail(CRM_ERR_INVALID, "null argument");
     CK(cudaSetDevice(s->device));
+    {
+        int rc = crm_refresh_bounds(s);
+        if (rc) return rc;
+    }
     uint32_t n = 0;
     const float lo = side == 0 ? -INFINITY : s->slab_hi - width;
     const float hi = side == 0 ? s->slab_lo + width : INFINITY;
@@ -261,6 +270,10 @@ int crm_sim_halo_pack_msgs(crm_sim* s, float width, void* dev_msg_lo, void* dev_
     if (!s) return crm_fail(CRM_ERR_INVALID, "null argument");
     CK(cudaSetDevice(s->device));
     void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    if (reselect || s->halo_sel_cap < cap) {
+        int rc = crm_refresh_bounds(s);  // the bands are selected on the centroids; records carry the bounds
+        if (rc) return rc;
+    }
     if (s->halo_sel_cap < cap) {
         for (int side = 0; side < 2; ++side) {
             if (s->halo_sel[side]) CK(cudaFree(s->halo_sel[side]));
@@ -304,6 +317,10 @@ int crm_sim_halo_pack_msgs(crm_sim* s, float width, void* dev_msg_lo, void* dev_
 int crm_sim_pack_leavers(crm_sim* s, void* dev_buf, uint32_t cap, uint32_t* n_out) {
     if (!s || !n_out) return crm_fail(CRM_ERR_INVALID, "null argument");
     CK(cudaSetDevice(s->device));
+    {
+        int rc = crm_refresh_bounds(s);
+        if (rc) return rc;
+    }
     uint32_t total = 0;
     for (int side = 0; side < 2; ++side) {
         if ((side == 0 && !(s->slab_lo > -INFINITY)) || (side == 1 && !(s->slab_hi < INFINITY))) continue;
@@ -373,6 +390,10 @@ int crm_sim_migrate_out(crm_sim* s, void* host_lo, uint32_t cap_lo, uint32_t* n_
     CK(cudaSetDevice(s->device));
     *n_lo_out = *n_hi_out = 0;
     if (s->n == 0) return 0;
+    {
+        int rc = crm_refresh_bounds(s);
+        if (rc) return rc;
+    }
     const int W = state_words(s->lp);
     const size_t rec = (size_t)W * 4 + sizeof(HostTail);
     std::vector<uint32_t> leaving;  // slots, lower-bound leavers first
@@ -461,6 +482,7 @@ int crm_sim_migrate_out(crm_sim* s, void* host_lo, uint32_t cap_lo, uint32_t* n_
     int rc = crm_read_status(s);
     if (rc) return rc;
     s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    s->bounds_fresh = true;
     return 0;
 }
 
@@ -508,6 +530,7 @@ int crm_sim_migrate_in(crm_sim* s, const void* host_buf, uint32_t n_in) {
     CK(cudaGetLastError());
     if ((rc = crm_read_status(s))) return rc;
     s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    s->bounds_fresh = true;
     return 0;
 }
 

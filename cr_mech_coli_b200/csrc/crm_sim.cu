@@ -229,7 +229,7 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     s->n = n0 + n_div;
     s->n_ghost = 0;  // the new cells took the first ghost slots; ghosts are re-sent every step
     s->d.n = s->d.n_own = s->n;
-    s->emax = std::max(s->emax, __builtin_bit_cast(float, s->h_status->emax_bits));
+    s->bounds_fresh = false;
     s->h_div.clear();
     s->pending_div = 0;
     s->need_rebuild = true;
@@ -257,9 +257,27 @@ static int handle_divisions(crm_sim* s, uint32_t n_div) {
     return crm_apply_divisions(s, idm.data(), idd.data(), gs.data());
 }
 
-static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false) {
-    int rc = configure_grid(s);
+// Bounds of the search (bounding sphere, chord, cull thresholds, max extent) for the current
+// positions.  The integrator only maintains the vertex records, so this runs before every search.
+int crm_refresh_bounds(crm_sim* s) {
+    if (s->bounds_fresh || s->n == 0) return 0;
+    s->d.n_own = s->n;
+    s->d.rsearch = search_radius(s);
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    launch_bounds_kernel(s->nv, s->d, s->stream);
+    s->launches += 1;
+    CK(cudaGetLastError());
+    int rc = crm_read_status(s);
     if (rc) return rc;
+    s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+    s->bounds_fresh = true;
+    return 0;
+}
+
+static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false) {
+    int rc = crm_refresh_bounds(s);
+    if (rc) return rc;
+    if ((rc = configure_grid(s))) return rc;
     s->d.n = s->n + s->n_ghost;
     s->d.n_own = s->n;
     s->d.rsearch = search_radius(s);
@@ -321,6 +339,7 @@ static int step_once(crm_sim* s) {
     if (rc) return rc;
     s->steps_since_build += 1;
     launch_integrate(s->nv, s->d, s->stream);
+    s->bounds_fresh = false;
     s->launches += 1;
     CK(cudaGetLastError());
     if ((rc = crm_read_status(s))) return rc;
@@ -331,7 +350,6 @@ static int step_once(crm_sim* s) {
         s->force_launches += 1;
     }
     if ((rc = crm_report_device_error(s))) return rc;
-    s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);  // owned rods; ghosts are re-sent before the next step
     const uint32_t n_div = s->h_status->n_div;
     bool want = n_div > 0 || s->h_status->n_leave > 0;
     if (persistent(s)) {
@@ -578,6 +596,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         CK(cudaGetLastError());
         if ((rc = crm_read_status(s))) return rc;
         s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
+        s->bounds_fresh = true;
         if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite initial positions");
     }
     return 0;

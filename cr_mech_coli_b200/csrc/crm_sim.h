@@ -63,6 +63,7 @@ struct crm_sim {
     float emax_ghost = 0.0f;  // ... over the current ghost rods
     float rsearch = 0.0f;
     bool fast_math = true;
+    bool bounds_fresh = false;  // bsphere / chord / cull thresholds / emax describe the current positions
     // persistent neighbour structure (Verlet lists): valid until a vertex moved more than skin/2
     float skin = 0.5f;          // um; 0 disables the structure (every step searches from scratch)
     bool need_rebuild = true;   // the next step must search (and rebuild the structure)
@@ -106,6 +107,7 @@ struct crm_sim {
 
 // shared host helpers (crm_sim.cu)
 int crm_take_snapshot(crm_sim* s);
+int crm_refresh_bounds(crm_sim* s);
 int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident* id_daughter, const uint64_t* gslot_daughter);
 void crm_fill_device_params(const crm_rod_params& p, crm::PotParams& pot, crm::MechParams& mech, crm::GrowState& grow,
                             crm::CycleParams& cyc);

@@ -206,6 +206,7 @@ class Shard:
                                                self.halo_cap, 0, 0, None, None))
             L.fn("sim_keep_lists")(h)
             return out
+        L.check(L.fn("sim_refresh_bounds")(h))  # centroids / extents of the current positions
         if self.n_leave:
             n = C.c_uint32(0)
             L.check(L.fn("sim_pack_leavers")(h, C.c_void_p(self.selfbuf.data_ptr()), self.halo_cap, C.byref(n)))
@@ -514,7 +515,7 @@ class DistributedShard:
         self.tr.sendrecv(s.send, s.recv)
         counts, incoming, emax = s.install_ghosts()
         self.last_counts = counts
-        self.emax_global = max(emax, s.max_extent())
+        self.emax_global = max(emax, s.max_extent())  # (refreshed on rebuild steps)
         # migrants travel only between neighbours that announced them in the message headers
         sides = [bool(len(out[k])) or incoming[k] for k in (0, 1)]
         self.moved = any(sides)  # the hand-over ghosts exist for this step only: rebuild again next step

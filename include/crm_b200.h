@@ -221,7 +221,10 @@ int crm_sim_set_global_slots(crm_sim* sim, const uint64_t* gslots, uint32_t n);
 int crm_sim_get_global_slots(const crm_sim* sim, uint64_t* out);
 uint32_t crm_sim_halo_record_bytes(const crm_sim* sim);
 uint32_t crm_sim_migrant_record_bytes(const crm_sim* sim);
-float crm_sim_max_extent(const crm_sim* sim);    /* max centroid->vertex distance over owned rods */
+float crm_sim_max_extent(const crm_sim* sim);
+/* The integrator maintains vertex records only; bounding data (centroids, extents) is recomputed
+ * before every search.  Call this before reading crm_sim_max_extent for a new halo selection. */
+int crm_sim_refresh_bounds(crm_sim* sim);    /* max centroid->vertex distance over owned rods */
 float crm_sim_search_radius(const crm_sim* sim); /* max interaction range over owned rods */
 /* Halo records of the owned rods whose centroid lies within `width` of the lower (side 0) /
  * upper (side 1) slab edge, in slot order, into dev_buf (capacity `cap` records). */
