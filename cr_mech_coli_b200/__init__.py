@@ -9,7 +9,7 @@ from .datatypes import (AgentSettings, CellIdentifier, Configuration, GrowthRate
                         MorsePotentialF32, PhysicalInteraction, RodAgent, RodMechanicsSettings,
                         SpringLengthThresholdSetter, StorageOption, VoxelPlainIndex)
 from .simulation import (SimulationError, generate_agents, generate_positions, run_simulation_with_agents,
-                         sort_cellular_identifiers)
+                         run_simulations_batched, sort_cellular_identifiers)
 
 # reference src/lib.rs:38-43,109-111
 MINUTE = 1.0

@@ -127,6 +127,9 @@ class Library:
             "sim_create": (C.c_int, [P(CrmConfig), C.c_int, P(vp)]),
             "sim_destroy": (None, [vp]),
             "sim_set_agents": (C.c_int, [vp, vp, vp, vp, u32, u32]),
+            "sim_set_agents_batched": (C.c_int, [vp, vp, vp, vp, vp, u32, u32, u32]),
+            "sim_get_sim_index": (C.c_int, [vp, vp]),
+            "sim_snapshot_sim_index": (C.c_int, [vp, u32, vp]),
             "sim_run": (C.c_int, [vp]),
             "sim_step": (C.c_int, [vp, u32]),
             "sim_compute_forces": (C.c_int, [vp, vp, vp]),
@@ -244,6 +247,31 @@ class Sim:
             raise ValueError("pos/vel must be (n_rods, n_vertices, 3) and params (n_rods,)")
         n, nv = pos.shape[0], pos.shape[1]
         self.L.check(self.L.fn("sim_set_agents")(self.h, _fptr(pos), _fptr(vel), _fptr(params), n, nv))
+
+    def set_agents_batched(self, pos, vel, params, sim_of, n_sims: int):
+        """Independent simulations in one device state: ``sim_of[a]`` = simulation of rod a."""
+        pos = np.ascontiguousarray(pos, dtype=np.float32)
+        vel = np.ascontiguousarray(vel, dtype=np.float32)
+        params = np.ascontiguousarray(params, dtype=ROD_PARAMS_DTYPE)
+        sim_of = np.ascontiguousarray(sim_of, dtype=np.uint32)
+        if pos.ndim != 3 or pos.shape[2] != 3 or vel.shape != pos.shape or params.shape[0] != pos.shape[0] or \
+                sim_of.shape[0] != pos.shape[0]:
+            raise ValueError("pos/vel must be (n_rods, n_vertices, 3), params and sim_of (n_rods,)")
+        self.L.check(self.L.fn("sim_set_agents_batched")(self.h, _fptr(pos), _fptr(vel), _fptr(params), _fptr(sim_of),
+                                                         pos.shape[0], pos.shape[1], int(n_sims)))
+
+    def snapshots_by_sim(self, n_sims: int):
+        """Per simulation: list of (iteration, pos, vel, params, ids, parents), rods in slot order."""
+        out = [[] for _ in range(n_sims)]
+        for k, (it, pos, vel, par, ids, parents) in enumerate(self.snapshots()):
+            so = np.zeros(len(pos), dtype=np.uint32)
+            self.L.check(self.L.fn("sim_snapshot_sim_index")(self.h, k, _fptr(so)))
+            order = np.argsort(so, kind="stable")
+            cuts = np.searchsorted(so[order], np.arange(n_sims + 1))
+            for m in range(n_sims):
+                sel = order[cuts[m]:cuts[m + 1]]
+                out[m].append((it, pos[sel], vel[sel], par[sel], ids[sel], parents[sel]))
+        return out
 
     @property
     def n_rods(self) -> int:

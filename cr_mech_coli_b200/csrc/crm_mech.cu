@@ -68,6 +68,7 @@ __global__ void k_bin_count(Dev d) {
     if (a >= d.n) return;
     float4 bs = d.bsphere[a];
     int c = cell_index(d, bs.x, bs.y);
+    if (d.tile) c += (int)(d.tile[a] * d.cpt);
     d.cell_of[a] = (uint32_t)c;
     d.cell_rank[a] = atomicAdd(&d.cell_count[c], 1u);
 }
@@ -499,6 +500,7 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
         d.cyc[b] = cp;
         d.nn[b] = d.nn[a];
         d.nhist[b] = 0;
+        if (d.tile) d.tile[b] = d.tile[a];
         atomicMax(&d.status->emax_bits, __float_as_uint(fmaxf(ext1, ext2)));
     }
 }
@@ -528,9 +530,9 @@ void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st) {
     CRM_NV_LIST(X)
 #undef X
 }
-int launch_binning(const Dev& d, cudaStream_t st) {
+int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st) {
     if (d.n == 0) return 0;
-    uint32_t ncells = (uint32_t)d.ncx * (uint32_t)d.ncy;
+    uint32_t ncells = (uint32_t)d.ncx * (uint32_t)d.ncy * n_tiles;
     cudaMemsetAsync(d.cell_count, 0, sizeof(uint32_t) * ncells, st);
     k_bin_count<<<blocks_for(d.n, 256), 256, 0, st>>>(d);
     k_bin_scan<<<1, 1024, 0, st>>>(d, ncells);

@@ -53,6 +53,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.grow, on, (size_t)cap);
     G(s->d.cyc, on, (size_t)cap);
     G(s->d.nn, on, (size_t)cap);
+    G(s->tile_buf, on, (size_t)cap);
     G(s->d.bsphere, on, (size_t)cap);
     G(s->d.chord, 2 * on, (size_t)2 * cap);
     G(s->d.vrec, on * s->lp, (size_t)cap * s->lp);
@@ -73,6 +74,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->stage, 0, (size_t)cap * s->nv * 3);
 #undef G
     s->d.divcap = cap;
+    s->d.tile = s->sim_of.empty() ? nullptr : s->tile_buf;
     s->cap = cap;
     return 0;
 }
@@ -100,8 +102,8 @@ static int configure_grid(crm_sim* s) {
     double ncx = std::floor((double)s->cfg.domain_size[0] / h), ncy = std::floor((double)s->cfg.domain_size[1] / h);
     if (!(ncx >= 1.0)) ncx = 1.0;
     if (!(ncy >= 1.0)) ncy = 1.0;
-    const double MAXC = 4.0 * 1024 * 1024;
-    while (ncx * ncy > MAXC) {
+    const double MAXC = 4.0 * 1024 * 1024 / (double)s->n_sims;  // batched sims: one tile of cells per sim
+    while (ncx * ncy > MAXC && ncx * ncy > 1.0) {
         ncx = std::max(1.0, std::floor(ncx / 1.5));
         ncy = std::max(1.0, std::floor(ncy / 1.5));
     }
@@ -109,7 +111,8 @@ static int configure_grid(crm_sim* s) {
     s->d.ncy = (int)ncy;
     s->d.inv_wx = (float)(ncx / (double)s->cfg.domain_size[0]);
     s->d.inv_wy = (float)(ncy / (double)s->cfg.domain_size[1]);
-    return reserve_cells(s, (uint32_t)(ncx * ncy));
+    s->d.cpt = (uint32_t)(ncx * ncy);
+    return reserve_cells(s, (uint32_t)(ncx * ncy) * s->n_sims);
 }
 
 // ------------------------------------------------------------------------------------
@@ -225,6 +228,7 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
         s->parents[b] = mother;
         s->base[b] = s->base[a];
         s->gslot[b] = gslot_daughter[r];
+        if (!s->sim_of.empty()) s->sim_of.push_back(s->sim_of[a]);  // b == sim_of.size(): slots are appended in order
     }
     s->n = n0 + n_div;
     s->n_ghost = 0;  // the new cells took the first ghost slots; ghosts are re-sent every step
@@ -242,18 +246,23 @@ static int handle_divisions(crm_sim* s, uint32_t n_div) {
     if (rc) return rc;
     const uint32_t n0 = s->n;
     const uint32_t nvox = s->cfg.n_voxels[0] * s->cfg.n_voxels[1];
-    std::vector<uint32_t> per_vox(nvox, 0), rank_vox(nvox, 0);
-    for (uint32_t r = 0; r < n_div; ++r) per_vox[s->h_div[r].uvox]++;
+    const bool batched = !s->sim_of.empty();
+    // counters are per (sim, user voxel); mothers come ordered by slot, which inside a sim is the
+    // slot order of that sim run on its own
+    auto key = [&](uint32_t r) { return (size_t)(batched ? s->sim_of[s->h_div[r].slot] : 0u) * nvox + s->h_div[r].uvox; };
+    std::vector<uint32_t> per_vox((size_t)nvox * s->n_sims, 0), rank_vox((size_t)nvox * s->n_sims, 0);
+    for (uint32_t r = 0; r < n_div; ++r) per_vox[key(r)]++;
     std::vector<crm_ident> idm(n_div), idd(n_div);
     std::vector<uint64_t> gs(n_div);
     for (uint32_t r = 0; r < n_div; ++r) {
         const uint32_t v = s->h_div[r].uvox;
-        const uint32_t k = rank_vox[v]++;
-        idm[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + 1 + k};
-        idd[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[v] + per_vox[v] + 1 + k};
-        gs[r] = (uint64_t)n0 + r;
+        const size_t kv = key(r);
+        const uint32_t k = rank_vox[kv]++;
+        idm[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[kv] + 1 + k};
+        idd[r] = crm_ident{CRM_ID_DIVISION, v, s->vox_counter[kv] + per_vox[kv] + 1 + k};
+        gs[r] = batched ? s->sim_rods[s->sim_of[s->h_div[r].slot]]++ : (uint64_t)n0 + r;
     }
-    for (uint32_t v = 0; v < nvox; ++v) s->vox_counter[v] += 2ull * per_vox[v];
+    for (size_t kv = 0; kv < per_vox.size(); ++kv) s->vox_counter[kv] += 2ull * per_vox[kv];
     return crm_apply_divisions(s, idm.data(), idd.data(), gs.data());
 }
 
@@ -283,7 +292,7 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
     s->d.rsearch = search_radius(s);
     s->d.skin = s->skin;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
-    s->launches += launch_binning(s->d, s->stream);
+    s->launches += launch_binning(s->d, s->n_sims, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
     launch_force(s->nv, s->d, s->fast_math, count, build, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
@@ -416,6 +425,7 @@ int crm_take_snapshot(crm_sim* s) {
     sn.ids.assign(s->ids.begin(), s->ids.begin() + s->n);
     sn.parents.assign(s->parents.begin(), s->parents.begin() + s->n);
     sn.gslot.assign(s->gslot.begin(), s->gslot.begin() + s->n);
+    sn.sim_of = s->sim_of;
     return download_state(s, sn.pos.data(), sn.vel.data(), sn.par.data());
 }
 
@@ -500,7 +510,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -551,6 +561,11 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->gslot.resize(n);
     s->n_ghost = 0;
     s->pending_div = 0;
+    s->sim_of.clear();
+    s->sim_rods.clear();
+    s->n_sims = 1;
+    s->d.tile = nullptr;
+    s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1], 0);
     std::vector<PotParams> pot(n);
     std::vector<MechParams> mech(n);
     std::vector<GrowState> grow(n);
@@ -599,6 +614,45 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         s->bounds_fresh = true;
         if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite initial positions");
     }
+    return 0;
+}
+
+// Batched independent sims (crm_fit ensembles, reference src/crm_fit/optimize.rs:75-95 runs one
+// run_simulation_with_agents per parameter point): all rods live in one device state, every sim is
+// a tile of the cell list, so rods of different sims never interact; identifiers, voxel counters
+// and snapshots are kept per sim.
+int crm_sim_set_agents_batched(crm_sim* s, const float* pos, const float* vel, const crm_rod_params* par,
+                               const uint32_t* sim_of, uint32_t n, uint32_t nv, uint32_t n_sims) {
+    if (!s || !sim_of || n_sims == 0) return fail(CRM_ERR_INVALID, "null argument");
+    if (s->sharded) return fail(CRM_ERR_INVALID, "batched sims cannot be sharded (replicas only)");
+    for (uint32_t a = 0; a < n; ++a)
+        if (sim_of[a] >= n_sims) return fail(CRM_ERR_INVALID, "rod %u: sim index %u out of range", a, sim_of[a]);
+    int rc = crm_sim_set_agents(s, pos, vel, par, n, nv);
+    if (rc) return rc;
+    s->n_sims = n_sims;
+    s->sim_of.assign(sim_of, sim_of + n);
+    s->sim_rods.assign(n_sims, 0);
+    s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1] * n_sims, 0);
+    for (uint32_t a = 0; a < n; ++a) {  // Initial(index inside the own sim)
+        const uint64_t k = s->sim_rods[sim_of[a]]++;
+        s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, k};
+        s->gslot[a] = k;
+    }
+    if (n) CK(cudaMemcpyAsync(s->tile_buf, sim_of, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    s->d.tile = s->tile_buf;
+    return 0;
+}
+
+int crm_sim_get_sim_index(const crm_sim* s, uint32_t* out) {
+    for (uint32_t a = 0; a < s->n; ++a) out[a] = s->sim_of.empty() ? 0u : s->sim_of[a];
+    return 0;
+}
+
+int crm_sim_snapshot_sim_index(const crm_sim* s, uint32_t k, uint32_t* out) {
+    if (k >= s->snaps.size()) return fail(CRM_ERR_INVALID, "snapshot %u out of range", k);
+    const HostSnap& sn = s->snaps[k];
+    for (uint32_t a = 0; a < sn.n; ++a) out[a] = sn.sim_of.empty() ? 0u : sn.sim_of[a];
     return 0;
 }
 

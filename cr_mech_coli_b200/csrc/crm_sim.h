@@ -19,7 +19,7 @@ int lanes_per_rod(int nv);
 void launch_unpack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
 void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t st);
 void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
-int launch_binning(const Dev& d, cudaStream_t st);
+int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st);
 void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
 void launch_force_eval(int nv, const Dev& d, bool fast, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
@@ -46,6 +46,7 @@ struct HostSnap {
     std::vector<crm_rod_params> par;
     std::vector<crm_ident> ids, parents;
     std::vector<uint64_t> gslot;
+    std::vector<uint32_t> sim_of;
 };
 
 struct crm_sim {
@@ -81,7 +82,11 @@ struct crm_sim {
     std::vector<crm_rod_params> base;  // cold fields per slot
     std::vector<crm_ident> ids, parents;
     std::vector<uint64_t> gslot;       // global slot (= slot of the unsharded run) per owned slot
-    std::vector<uint64_t> vox_counter;
+    std::vector<uint64_t> vox_counter;   // [sim][user voxel]
+    std::vector<uint32_t> sim_of;        // batched sims: sim index per slot (empty: one colony)
+    uint32_t n_sims = 1;
+    uint32_t* tile_buf = nullptr;        // device copy of sim_of (Dev::tile points here when batched)
+    std::vector<uint64_t> sim_rods;      // batched sims: rods ever created per sim (next local slot)
     std::vector<crm::DivRecord> h_div;
     uint64_t iteration = 0, rod_steps = 0, launches = 0;
     std::vector<uint64_t> save_iter;

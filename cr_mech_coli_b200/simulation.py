@@ -85,6 +85,29 @@ def run_simulation_with_agents(config: Configuration, agents, device: int = 0) -
     return CellContainer(path=None, _snapshots=snaps)
 
 
+def run_simulations_batched(config: Configuration, agent_lists, device: int = 0):
+    """Many independent ``run_simulation_with_agents(config, agents)`` calls in ONE device state
+    (parameter-fitting ensembles: reference src/crm_fit/predict.rs:231-287 run once per parameter
+    point by src/crm_fit/optimize.rs:75-95).  Returns one ``CellContainer`` per agent list, equal to
+    what the individual calls return (deterministic settings)."""
+    unsupported = [o for o in config.storage_options if o != StorageOption.Memory]
+    if unsupported:
+        raise NotImplementedError(f"storage options {unsupported} are not implemented (Memory only)")
+    agent_lists = [list(a) for a in agent_lists]
+    n_sims = len(agent_lists)
+    flat = [a for lst in agent_lists for a in lst]
+    if not flat:
+        return [run_simulation_with_agents(config, [], device) for _ in agent_lists]
+    sim_of = np.concatenate([np.full(len(lst), m, np.uint32) for m, lst in enumerate(agent_lists)])
+    lib = _capi.product()
+    pos, vel, par = pack_agents(flat)
+    with _capi.Sim(lib, config._to_c(), device) as sim:
+        sim.set_agents_batched(pos, vel, par, sim_of, n_sims)
+        sim.run()
+        per_sim = sim.snapshots_by_sim(n_sims)
+    return [CellContainer(path=None, _snapshots=[_Snapshot(*s) for s in snaps]) for snaps in per_sim]
+
+
 def sort_cellular_identifiers(identifiers):
     """reference src/simulation.rs:332-339"""
     return sorted(identifiers)

@@ -144,6 +144,17 @@ void crm_sim_destroy(crm_sim* sim);
 int crm_sim_set_agents(crm_sim* sim, const float* pos, const float* vel,
                        const crm_rod_params* params, uint32_t n_rods, uint32_t n_vertices);
 
+/* Batched independent simulations in one device state (parameter-fitting ensembles: the reference
+ * runs one run_simulation_with_agents per parameter point, src/crm_fit/predict.rs:231-287, fanned out
+ * by rayon / scipy workers, src/crm_fit/optimize.rs:75-95,235-252).  sim_of[a] = simulation of rod a;
+ * rods of different simulations never interact; identifiers, per-voxel counters and snapshots are
+ * kept per simulation (crm_sim_snapshot_sim_index splits a snapshot).  All simulations share the
+ * Configuration. */
+int crm_sim_set_agents_batched(crm_sim* sim, const float* pos, const float* vel, const crm_rod_params* params,
+                               const uint32_t* sim_of, uint32_t n_rods, uint32_t n_vertices, uint32_t n_sims);
+int crm_sim_get_sim_index(const crm_sim* sim, uint32_t* out);
+int crm_sim_snapshot_sim_index(const crm_sim* sim, uint32_t k, uint32_t* out);
+
 /* The whole of `run_main!` (reference src/simulation.rs:283-292): steps to
  * t_max, snapshots at the save iterations into host memory owned by `sim`. */
 int crm_sim_run(crm_sim* sim);
