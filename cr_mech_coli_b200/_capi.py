@@ -177,6 +177,12 @@ class Library:
             "sim_skin": (C.c_float, [vp]),
             "sim_pack_leavers": (C.c_int, [vp, vp, u32, P(u32)]),
             "sim_set_ghosts_msgs": (C.c_int, [vp, vp, vp, vp, u32, vp, vp, P(C.c_float)]),
+            "sim_stream": (vp, [vp]),
+            "sim_set_stream": (C.c_int, [vp, vp]),
+            "sim_halo_repack": (C.c_int, [vp, vp, vp]),
+            "sim_ghosts_refresh": (C.c_int, [vp, vp, vp]),
+            "sim_step_begin": (C.c_int, [vp, vp]),
+            "sim_step_end": (C.c_int, [vp]),
             "sim_migrate_out": (C.c_int, [vp, vp, u32, P(u32), vp, u32, P(u32)]),
             "sim_migrate_in": (C.c_int, [vp, vp, u32]),
             "sim_n_leaving": (u32, [vp]),
@@ -378,7 +384,7 @@ def product() -> Library:
     global _PRODUCT
     if _PRODUCT is None:
         _PRODUCT = Library(_PKG_DIR / LIB_NAME, "crm_")
-        if _PRODUCT.fn("abi_version")() != 2:
+        if _PRODUCT.fn("abi_version")() != 3:
             raise ImportError("libcrm_b200.so: ABI version mismatch")
     return _PRODUCT
 

@@ -185,13 +185,15 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     constexpr int LP = Lay<NV>::LP;
     constexpr int STRIDE = Lay<NV>::STRIDE;
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t a = tid / LP;
     const int l = threadIdx.x % LP;
-    const unsigned gm = group_mask<LP>();
-    if (a >= d.n_own) return;
+    // the whole warp stays converged (full-mask shuffles: a per-group mask costs a uniform-register
+    // waterfall per shuffle); groups past the last rod recompute it and store nothing
+    const unsigned gm = 0xffffffffu;
+    const bool valid = tid / LP < d.n_own;
+    const uint32_t a = valid ? tid / LP : d.n_own - 1;
     const size_t o = (size_t)a * STRIDE;
-    const bool hv = l < NV;
-    const int li = hv ? l : 0;
+    const bool hv = valid && l < NV;
+    const int li = l < NV ? l : 0;
 
     float P[3], V[3], F[3];
 #pragma unroll
@@ -202,6 +204,24 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     }
     const MechParams mp = d.mech[a];
     GrowState gs = d.grow[a];
+    // every load of the step is issued here, before the first store (the stores below may alias as far
+    // as the compiler knows, and one DRAM round trip per vector component is what bounds this kernel)
+    const bool odd = (d.iteration & 1ull) != 0;
+    float* const newx = odd ? d.dx2 : d.dx1;  // increment history as a two-slot ring: written at step it-1
+    float* const newv = odd ? d.dv2 : d.dv1;
+    float* const oldx = odd ? d.dx1 : d.dx2;  // written at step it-2: read as the older increment, rewritten now
+    float* const oldv = odd ? d.dv1 : d.dv2;
+    float X1[3], V1[3], X2[3], V2[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const size_t i = o + c * LP + li;
+        X1[c] = newx[i]; V1[c] = newv[i]; X2[c] = oldx[i]; V2[c] = oldv[i];
+    }
+    const int nh = d.nhist[a];
+    const CycleParams cp = d.cyc[a];
+    const float nnb = cp.has_nr ? (float)d.nn[a] : 0.0f;
+    float4 vb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (d.vbuild) vb = d.vbuild[(size_t)a * LP + li];
     const float tension = mp.x, rigidity = mp.y, damping = mp.z, diffusion = mp.w;
     const float L = gs.z;
 
@@ -216,10 +236,13 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     float fs[3] = {0.f, 0.f, 0.f};
     float c2[3] = {P[0] - Pn[0], P[1] - Pn[1], P[2] - Pn[2]};  // conn_l = v_l - v_{l+1}
     float n2 = sqrtf(c2[0] * c2[0] + c2[1] * c2[1] + c2[2] * c2[2]);
+    // unit connections: correctly rounded quotients from one reciprocal per length (div_rn)
+    const float y2 = rcp_refined(n2);
+    const float u2[3] = {div_rn(c2[0], n2, y2), div_rn(c2[1], n2, y2), div_rn(c2[2], n2, y2)};
     if (l < NV - 1 && n2 != 0.0f) {
         float k = tension * (n2 - L);
 #pragma unroll
-        for (int c = 0; c < 3; ++c) fs[c] = -(c2[c] / n2) * k;
+        for (int c = 0; c < 3; ++c) fs[c] = -u2[c] * k;
     }
     // bending at interior vertex l
     float fb[3] = {0.f, 0.f, 0.f};
@@ -231,15 +254,18 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             if (n1 == 0.0f || n2 == 0.0f) {
                 angle = 0.0f;
             } else {
-                float cs = -(c1[0] * c2[0] + c1[1] * c2[1] + c1[2] * c2[2]) / (n1 * n2);
+                const float nn = n1 * n2;
+                float cs = div_rn(-(c1[0] * c2[0] + c1[1] * c2[1] + c1[2] * c2[2]), nn, rcp_refined(nn));
                 cs = fminf(fmaxf(cs, -1.0f), 1.0f);
                 angle = acosf(cs);
             }
-            float fd[3] = {c1[0] / n1 - c2[0] / n2, c1[1] / n1 - c2[1] / n2, c1[2] / n1 - c2[2] / n2};
+            const float y1 = rcp_refined(n1);
+            float fd[3] = {div_rn(c1[0], n1, y1) - u2[0], div_rn(c1[1], n1, y1) - u2[1], div_rn(c1[2], n1, y1) - u2[2]};
             float nfd = sqrtf(fd[0] * fd[0] + fd[1] * fd[1] + fd[2] * fd[2]);
             float scale = rigidity * (3.14159265358979323846f - angle);
+            const float yf = rcp_refined(nfd);
 #pragma unroll
-            for (int c = 0; c < 3; ++c) fb[c] = ((nfd == 0.0f) ? fd[c] : fd[c] / nfd) * scale;
+            for (int c = 0; c < 3; ++c) fb[c] = ((nfd == 0.0f) ? fd[c] : div_rn(fd[c], nfd, yf)) * scale;
         }
     }
     float dv[3];
@@ -260,22 +286,13 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         dv[c] = t;
     }
     // Adams-Bashforth over the stored increments
-    const int nh = d.nhist[a];
     const float dt = d.dt;
-    // increment history as a two-slot ring: the slot written two steps ago is read (as the older
-    // increment) and then overwritten with this step's increment
-    const bool odd = (d.iteration & 1ull) != 0;
-    float* const newx = odd ? d.dx2 : d.dx1;  // written at step it-1
-    float* const newv = odd ? d.dv2 : d.dv1;
-    float* const oldx = odd ? d.dx1 : d.dx2;  // written at step it-2, rewritten now
-    float* const oldv = odd ? d.dv1 : d.dv2;
     const float c23 = 23.0f / 12.0f, c16 = 16.0f / 12.0f, c5 = 5.0f / 12.0f;
     const float amp = (diffusion > 0.0f) ? sqrtf(2.0f * diffusion * dt) : 0.0f;
     float Pnew[3], Vnew[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        const size_t i = o + c * LP + li;
-        float x1 = newx[i], v1 = newv[i], x2 = oldx[i], v2 = oldv[i];
+        const float x1 = X1[c], v1 = V1[c], x2 = X2[c], v2 = V2[c];
         float ip, iv;
         if (nh >= 2) {
             ip = (c23 * V[c] - c16 * x1 + c5 * x2) * dt;
@@ -292,17 +309,13 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             normal_pair(d.seed, d.iteration, a, (uint64_t)(l * 3 + c), n0, n1);
             ip += amp * n0;
         }
-        if (hv) {
-            oldx[i] = V[c]; oldv[i] = dv[c];
-        }
         Pnew[c] = P[c] + ip;
         Vnew[c] = V[c] + iv;
     }
     // Cycle::update_cycle (bit-exact ops: no FMA contraction, same order as the reference)
     float rate = gs.x;
-    if (d.cyc[a].has_nr) {
-        const CycleParams cp = d.cyc[a];
-        float mx = (float)cp.nr_max, nnb = (float)d.nn[a];
+    if (cp.has_nr) {
+        const float mx = (float)cp.nr_max;
         rate = __fmul_rn(gs.x, powf(fmaxf(__fdiv_rn(__fsub_rn(mx, nnb), mx), 0.0f), cp.nr_exp));
     }
     const float newL = __fadd_rn(L, __fmul_rn(__fmul_rn(rate, dt), L));
@@ -320,6 +333,8 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         for (int c = 0; c < 3; ++c) {
             d.pos[o + c * LP + l] = Pnew[c];
             d.vel[o + c * LP + l] = Vnew[c];
+            oldx[o + c * LP + l] = V[c];
+            oldv[o + c * LP + l] = dv[c];
         }
         if (!finite || !inside) {
             if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
@@ -327,19 +342,18 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         }
     }
     if (d.vbuild) {  // displacement since the persistent neighbour structure was built
-        const float4 vb = d.vbuild[(size_t)a * LP + li];
         const float ex = Pnew[0] - vb.x, ey = Pnew[1] - vb.y, ez = Pnew[2] - vb.z;
         const float dd = group_max<LP>(hv ? ex * ex + ey * ey + ez * ez : 0.0f, gm);
-        if (l == 0) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
+        if (l == 0 && valid) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
     }
     // The bounds of the search (sphere, chord, cull thresholds) are recomputed by k_bounds only when a
     // search follows (rebuild steps); every step needs just the vertex record of the force kernel.
-    d.vrec[(size_t)a * LP + l] = make_float4(Pnew[0], Pnew[1], Pnew[2], -1.0f);
+    if (valid) d.vrec[(size_t)a * LP + l] = make_float4(Pnew[0], Pnew[1], Pnew[2], -1.0f);
     if (d.slab_lo > -INFINITY || d.slab_hi < INFINITY) {  // sharded: rods whose centroid left the slab
         const float cx = group_sum<LP>(hv ? Pnew[0] : 0.0f, gm) * (1.0f / NV);
-        if (l == 0 && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);
+        if (l == 0 && valid && !(cx >= d.slab_lo && cx < d.slab_hi)) atomicAdd(&d.status->n_leave, 1u);
     }
-    if (dividing) {
+    if (__any_sync(gm, dividing)) {  // (warp-uniform: the shuffles below need every lane)
         // user voxel of the mother = voxel of the mean vertex at the start of the step,
         // summed sequentially like the reference (nalgebra row_mean)
         float mx = 0.f, my = 0.f;
@@ -348,7 +362,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             mx = __fadd_rn(mx, __shfl_sync(gm, P[0], q, LP));
             my = __fadd_rn(my, __shfl_sync(gm, P[1], q, LP));
         }
-        if (l == 0) {
+        if (l == 0 && valid && dividing) {
             mx = __fdiv_rn(mx, (float)NV);
             my = __fdiv_rn(my, (float)NV);
             int ix = (int)floorf(__fdiv_rn(mx, d.uvx_w)), iy = (int)floorf(__fdiv_rn(my, d.uvy_w));
@@ -363,7 +377,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             }
         }
     }
-    if (l == 0) {
+    if (l == 0 && valid) {
         gs.z = newL;
         d.grow[a] = gs;
         if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
@@ -542,7 +556,13 @@ int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st) {
 }
 void launch_integrate(int nv, const Dev& d, cudaStream_t st) {
     if (d.n_own == 0) return;
-#define X(NVV) if (nv == NVV) k_integrate<NVV><<<blocks_for((uint64_t)d.n_own * Lay<NVV>::LP, 128), 128, 0, st>>>(d);
+    // Occupancy cap: measured on B200 (1e6 rods, 8 vertices) the kernel runs 0.297 ms at <= 26 resident
+    // warps per SM and 0.37-0.40 ms at >= 28 (its ~30 loads per warp are all issued up front; beyond that
+    // point the memory system thrashes).  A dynamic shared-memory reservation nobody touches keeps
+    // six 128-thread blocks = 24 warps per SM (36000 B: below the 48 KB that needs no opt-in).
+    constexpr int CAP_SMEM = 36000;
+#define X(NVV) \
+    if (nv == NVV) k_integrate<NVV><<<blocks_for((uint64_t)d.n_own * Lay<NVV>::LP, 128), 128, CAP_SMEM, st>>>(d);
     CRM_NV_LIST(X)
 #undef X
 }

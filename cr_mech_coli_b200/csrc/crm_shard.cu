@@ -312,6 +312,28 @@ int crm_sim_halo_pack_msgs(crm_sim* s, float width, void* dev_msg_lo, void* dev_
     return 0;
 }
 
+// The frozen selections of the last rebuild packed again, stream-ordered: nothing waits for the
+// device, the caller's transport has to run on crm_sim_stream (or wait for it).
+int crm_sim_halo_repack(crm_sim* s, void* dev_msg_lo, void* dev_msg_hi) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null argument");
+    if (!s->halo_sel_cap) return crm_fail(CRM_ERR_INVALID, "no halo selection yet (crm_sim_halo_pack_msgs with reselect)");
+    CK(cudaSetDevice(s->device));
+    void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    for (int side = 0; side < 2; ++side) {
+        if (!msg[side]) continue;
+        const uint32_t n = s->halo_sel_n[side];
+        k_write_header<<<1, 1, 0, s->stream>>>((uint32_t*)msg[side], s->halo_sel[side], s->emax, 0u);
+        if (n) {
+            const uint64_t threads = (uint64_t)n * (s->lp + 5);
+            k_halo_gather<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
+                s->d, s->halo_sel[side] + 1, n, s->lp, reinterpret_cast<float4*>((char*)msg[side] + 64));
+        }
+        s->launches += n ? 2 : 1;
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
 // Halo records of the owned rods whose centroid is OUTSIDE the slab (about to migrate): the old
 // owner keeps them as ghosts for the step in which the new owner has not announced them yet.
 int crm_sim_pack_leavers(crm_sim* s, void* dev_buf, uint32_t cap, uint32_t* n_out) {
@@ -373,11 +395,38 @@ int crm_sim_set_ghosts_msgs(crm_sim* s, const void* dev_msg_lo, const void* dev_
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(s->stream));  // the receive buffers may be reused by the caller
     s->n_ghost = n_lo + n_hi + n_self;
+    s->ghost_n[0] = n_lo;
+    s->ghost_n[1] = n_hi;
     if (n_self) emax = std::max(emax, s->emax);
     s->emax_ghost = emax;
     if (counts) { counts[0] = n_lo; counts[1] = n_hi; }
     if (flags) { flags[0] = h[2]; flags[1] = h[6]; }
     if (max_extent) *max_extent = emax;
+    return 0;
+}
+
+// The ghosts of a step between two rebuilds: both neighbours re-sent their frozen selections, so
+// the counts and ghost slots are those of the last crm_sim_set_ghosts_msgs.  Stream-ordered, the
+// headers are not read (a neighbour that reselected would have announced a rebuild to all slabs).
+int crm_sim_ghosts_refresh(crm_sim* s, const void* dev_msg_lo, const void* dev_msg_hi) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null sim");
+    if (s->pending_div) return crm_fail(CRM_ERR_INVALID, "divisions pending");
+    if (s->n_ghost != s->ghost_n[0] + s->ghost_n[1])
+        return crm_fail(CRM_ERR_INVALID, "the ghosts of the last rebuild step include hand-over records: rebuild first");
+    if ((s->ghost_n[0] && !dev_msg_lo) || (s->ghost_n[1] && !dev_msg_hi)) return crm_fail(CRM_ERR_INVALID, "missing halo message");
+    CK(cudaSetDevice(s->device));
+    const void* msg[2] = {dev_msg_lo, dev_msg_hi};
+    uint32_t first = s->n;
+    for (int side = 0; side < 2; ++side) {
+        const uint32_t n = s->ghost_n[side];
+        if (!n) continue;
+        const uint64_t threads = (uint64_t)n * (s->lp + 5);
+        k_ghost_scatter<<<blocks_for(threads, 256), 256, 0, s->stream>>>(
+            s->d, reinterpret_cast<const float4*>((const char*)msg[side] + 64), n, first, s->lp);
+        first += n;
+        s->launches += 1;
+    }
+    CK(cudaGetLastError());
     return 0;
 }
 

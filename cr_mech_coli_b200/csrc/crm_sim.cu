@@ -312,10 +312,25 @@ static int launch_force_from_lists(crm_sim* s) {
     return 0;
 }
 
-static int step_once(crm_sim* s) {
+// [n_div, reason to rebuild] of the step just enqueued, for the sharded coordinator's all_gather
+// (the same conditions step_finish evaluates on the host)
+__global__ void k_status_flags(const Status* st, float skin, uint32_t host_want, uint32_t* flags) {
+    const float disp = sqrtf(__uint_as_float(st->disp2_bits));
+    uint32_t want = host_want | (st->n_div > 0) | (st->n_leave > 0) | (st->err_code != 0);
+    if (skin > 0.0f) want |= (st->plist_overflow != 0) | !(disp < 0.4999f * skin);
+    flags[0] = st->n_div;
+    flags[1] = want ? 1u : 0u;
+}
+
+// A step is enqueued (step_enqueue: nothing waits for the device unless a search needs fresh bounds)
+// and finished (step_finish: one stream synchronisation, then the host's bookkeeping).
+static int step_enqueue(crm_sim* s, uint32_t* dev_flags) {
     if (s->pending_div) return fail(CRM_ERR_INVALID, "divisions of the last step are pending (crm_sim_apply_divisions)");
+    if (s->step_open) return fail(CRM_ERR_INVALID, "the last step was not finished (crm_sim_step_end)");
+    s->step_open = true;
     if (s->n == 0) {
         s->iteration += 1;
+        if (dev_flags) CK(cudaMemsetAsync(dev_flags, 0, 2 * sizeof(uint32_t), s->stream));
         return 0;
     }
     s->iteration += 1;
@@ -350,8 +365,21 @@ static int step_once(crm_sim* s) {
     launch_integrate(s->nv, s->d, s->stream);
     s->bounds_fresh = false;
     s->launches += 1;
+    if (dev_flags) {
+        k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, persistent(s) ? s->skin : 0.0f, s->have_lists ? 0u : 1u, dev_flags);
+        s->launches += 1;
+    }
     CK(cudaGetLastError());
-    if ((rc = crm_read_status(s))) return rc;
+    CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    return 0;
+}
+
+static int step_finish(crm_sim* s) {
+    if (!s->step_open) return 0;
+    s->step_open = false;
+    if (s->n == 0) return 0;
+    int rc;
+    CK(cudaStreamSynchronize(s->stream));
     if (s->timers) {
         float ms = 0.0f;
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
@@ -381,6 +409,15 @@ static int step_once(crm_sim* s) {
         }
     }
     return 0;
+}
+
+static int step_once(crm_sim* s) {
+    int rc = step_enqueue(s, nullptr);
+    if (rc) {
+        s->step_open = false;
+        return rc;
+    }
+    return step_finish(s);
 }
 
 static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
@@ -518,7 +555,8 @@ void crm_sim_destroy(crm_sim* s) {
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_t0) cudaEventDestroy(s->ev_t0);
     if (s->ev_t1) cudaEventDestroy(s->ev_t1);
-    if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->stream && s->own_stream) cudaStreamDestroy(s->stream);
     delete s;
 }
 
@@ -663,6 +701,38 @@ int crm_sim_step(crm_sim* s, uint32_t n_steps) {
         if (rc) return rc;
     }
     return 0;
+}
+
+// The step in two halves for callers that order their own work (halo transport, collectives) on
+// the sim's stream: begin enqueues the step and writes [n_div, reason to rebuild] to dev_flags on
+// the stream; end waits for the stream once and does the host's part of the step.
+void* crm_sim_stream(const crm_sim* s) { return s ? (void*)s->stream : nullptr; }
+
+// Run on a stream the caller owns (e.g. one of torch's pool streams, so that tensors used with it
+// never outlive it); the sim's own stream is released.
+int crm_sim_set_stream(crm_sim* s, void* stream) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    if (s->step_open) return fail(CRM_ERR_INVALID, "a step is in flight");
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize(s->stream));
+    if (s->own_stream && s->stream) CK(cudaStreamDestroy(s->stream));
+    s->stream = (cudaStream_t)stream;
+    s->own_stream = false;
+    return 0;
+}
+
+int crm_sim_step_begin(crm_sim* s, uint32_t* dev_flags) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    CK(cudaSetDevice(s->device));
+    int rc = step_enqueue(s, dev_flags);
+    if (rc) s->step_open = false;
+    return rc;
+}
+
+int crm_sim_step_end(crm_sim* s) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    CK(cudaSetDevice(s->device));
+    return step_finish(s);
 }
 
 int crm_sim_step_timed(crm_sim* s, uint32_t n_steps, double* ms_out) {

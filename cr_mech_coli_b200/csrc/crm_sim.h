@@ -94,6 +94,9 @@ struct crm_sim {
     std::vector<HostSnap> snaps;
     // sharding (crm_shard.cu)
     bool sharded = false;      // divisions are deferred to crm_sim_apply_divisions
+    bool own_stream = true;    // false after crm_sim_set_stream
+    bool step_open = false;    // crm_sim_step_begin enqueued a step that crm_sim_step_end has not finished
+    uint32_t ghost_n[2] = {0, 0};  // ghosts installed from the lower / upper message (crm_sim_ghosts_refresh)
     float slab_lo = -INFINITY, slab_hi = INFINITY;
     uint32_t pending_div = 0;  // divisions of the last step awaiting crm_sim_apply_divisions
     void* select_tmp = nullptr;  // cub temp storage

@@ -20,12 +20,16 @@ is exercised on CPU with ``gloo`` (tests/test_sharded_host.py); device work goes
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
 from . import _capi
 
 HEADER_BYTES = 64  # message header: int32 n_records, float32 max_extent
+# steps between two rebuilds run stream-ordered (no host wait between pack, transport, ghosts, step and
+# the flag all_gather); CRM_B200_SYNC_HALO=1 selects the synchronous protocol for comparison
+STREAM_ORDERED = os.environ.get("CRM_B200_SYNC_HALO", "0") != "1"
 
 
 # --------------------------------------------------------------------------------------------
@@ -153,8 +157,16 @@ class Shard:
         self.halo_cap = halo_cap
         self.msg = None
         self.emax_nb = 0.0
+        # the sim runs on one of torch's pool streams (they are never destroyed, so tensors recorded on it
+        # cannot outlive it): transport enqueued under it is ordered with the kernels
+        self.stream = torch.cuda.Stream(device=self.device)
+        lib.check(lib.fn("sim_set_stream")(self.sim.h, C.c_void_p(self.stream.cuda_stream)))
+        self.flags = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.n_send = [0, 0]
+        self.n_recv = [0, 0]
 
     def close(self):
+        self.torch.cuda.synchronize(self.device)
         self.sim.close()
 
     # -- setup ---------------------------------------------------------------
@@ -171,6 +183,7 @@ class Shard:
         self.send = [t.zeros(HEADER_BYTES + self.halo_cap * self.rb, dtype=t.uint8, device=self.device) for _ in range(2)]
         self.recv = [t.zeros_like(self.send[0]) for _ in range(2)]
         self.selfbuf = t.zeros(self.halo_cap * self.rb, dtype=t.uint8, device=self.device)
+        t.cuda.synchronize(self.device)  # (filled on torch's current stream, used on the sim's)
         self.n_self = 0
         self.n_leave = 0
         g = np.asarray(par["growth_rate"]) if len(gs) else np.zeros(0)
@@ -217,8 +230,38 @@ class Shard:
         width = self.halo_width(max(emax_nb, self.max_extent()))
         lo = C.c_void_p(self.send[0].data_ptr()) if self.rank > 0 else None
         hi = C.c_void_p(self.send[1].data_ptr()) if self.rank + 1 < self.partition.world else None
-        L.check(L.fn("sim_halo_pack_msgs")(h, width, lo, hi, self.halo_cap, flags, 1, None, None))
+        n_lo, n_hi = C.c_uint32(0), C.c_uint32(0)
+        L.check(L.fn("sim_halo_pack_msgs")(h, width, lo, hi, self.halo_cap, flags, 1, C.byref(n_lo), C.byref(n_hi)))
+        self.n_send = [int(n_lo.value) if lo else 0, int(n_hi.value) if hi else 0]
         return out
+
+    def _msg_ptrs(self, bufs):
+        return (C.c_void_p(bufs[0].data_ptr()) if self.rank > 0 else None,
+                C.c_void_p(bufs[1].data_ptr()) if self.rank + 1 < self.partition.world else None)
+
+    def frozen_pack(self):
+        """Stream-ordered half of a step between rebuilds: the frozen selections packed again (no
+        host wait).  Returns the message slices to send / receive (the counts are those of the last
+        rebuild step on both ends)."""
+        L, h = self.lib, self.sim.h
+        L.check(L.fn("sim_halo_repack")(h, *self._msg_ptrs(self.send)))
+        L.fn("sim_keep_lists")(h)
+        self.n_self = 0
+        cut = lambda bufs, n: [b[:HEADER_BYTES + k * self.rb] if (side == 0 and self.rank > 0) or
+                               (side == 1 and self.rank + 1 < self.partition.world) else b[:0]
+                               for side, (b, k) in enumerate(zip(bufs, n))]
+        return cut(self.send, self.n_send), cut(self.recv, self.n_recv)
+
+    def frozen_ghosts(self):
+        self.lib.check(self.lib.fn("sim_ghosts_refresh")(self.sim.h, *self._msg_ptrs(self.recv)))
+
+    def step_begin(self):
+        """Enqueue the step; ``self.flags`` (device int32[2]) receives [divisions, reason to rebuild]."""
+        self.lib.check(self.lib.fn("sim_step_begin")(self.sim.h, C.c_void_p(self.flags.data_ptr())))
+
+    def step_end(self):
+        self.lib.check(self.lib.fn("sim_step_end")(self.sim.h))
+        return self._step_result()
 
     def install_ghosts(self):
         """Ghosts of this step from the received messages + the own leavers.  Returns (counts,
@@ -233,12 +276,16 @@ class Shard:
                                             C.byref(emax)))
         # the lower neighbour announces migrants for us in bit 1 (its upper side), the upper one in bit 0
         incoming = (bool(flags[0] & 2), bool(flags[1] & 1))
+        self.n_recv = [int(counts[0]), int(counts[1])]
         return (int(counts[0]), int(counts[1])), incoming, float(emax.value)
 
     # -- step ----------------------------------------------------------------
     def step_local(self):
         """One local step; returns (pending divisions, 1 if this slab has a reason to rebuild)."""
         self.sim.step(1)
+        return self._step_result()
+
+    def _step_result(self):
         n_div = int(self.lib.fn("sim_pending_divisions")(self.sim.h, None, None, 0))
         self.n_leave = int(self.lib.fn("sim_n_leaving")(self.sim.h))
         return n_div, int(self.lib.fn("sim_wants_rebuild")(self.sim.h))
@@ -369,10 +416,35 @@ class LocalCluster:
             if got:  # the new owned rods took the first ghost slots
                 s.install_ghosts()
 
+    def _frozen_step(self):
+        """A step between two rebuilds through the stream-ordered entry points (the protocol the
+        distributed driver runs without host waits; here the copies need the streams joined)."""
+        t, w = self.shards[0].torch, len(self.shards)
+        cuts = [s.frozen_pack() for s in self.shards]
+        for s in self.shards:
+            s.stream.synchronize()
+        for r in range(w):
+            if r > 0:
+                cuts[r][1][0].copy_(cuts[r - 1][0][1])
+            if r + 1 < w:
+                cuts[r][1][1].copy_(cuts[r + 1][0][0])
+        t.cuda.synchronize()
+        for s in self.shards:
+            s.frozen_ghosts()
+            s.step_begin()
+        status = [s.step_end() for s in self.shards]
+        for s, st in zip(self.shards, status):  # the device-written flags are what the ranks all_gather
+            assert s.flags.tolist() == [st[0], int(bool(st[1]))], (s.flags.tolist(), st)
+        self.moved = False
+        return status
+
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
-            self._exchange_halos()
-            status = [s.step_local() for s in self.shards]
+            if STREAM_ORDERED and not self.rebuild_next:
+                status = self._frozen_step()
+            else:
+                self._exchange_halos()
+                status = [s.step_local() for s in self.shards]
             self.iteration += 1
             self.rebuild_next = any(w for _, w in status) or self.moved  # rebuilds are collective
             if any(nd for nd, _ in status):
@@ -422,9 +494,10 @@ class Transport:
     def neighbours(self):
         return (self.rank - 1 if self.rank > 0 else None, self.rank + 1 if self.rank + 1 < self.world else None)
 
-    def sendrecv(self, send, recv):
+    def sendrecv(self, send, recv, wait: bool = True):
         """send[0]/recv[0] <-> lower neighbour, send[1]/recv[1] <-> upper neighbour; empty tensors
-        are skipped (both sides know the sizes)."""
+        are skipped (both sides know the sizes).  ``wait=False`` (NCCL): the transfers are only
+        ordered on the current stream, the host does not wait."""
         dist, ops = self.dist, []
         for side, nb in enumerate(self.neighbours()):
             if nb is None:
@@ -436,7 +509,7 @@ class Transport:
         if ops:
             for w in dist.batch_isend_irecv(ops):
                 w.wait()
-            if self.device.type == "cuda":
+            if self.device.type == "cuda" and wait:
                 self.torch.cuda.current_stream(self.device).synchronize()
 
     def allgather(self, values) -> np.ndarray:
@@ -489,6 +562,7 @@ class DistributedShard:
         self.iteration = 0
         self.coord = None
         self.emax_global = 0.0
+        self._flags_all = self._flags_host = None
 
     def close(self):
         self.shard.close()
@@ -526,16 +600,39 @@ class DistributedShard:
             if any(len(r) for r in got):
                 s.install_ghosts()
 
+    def _frozen_step(self):
+        """A step between two rebuilds, enqueued on the sim's stream end to end: pack -> NCCL
+        send/recv -> ghost scatter -> force + integrate -> all_gather of the device-written
+        [divisions, rebuild] flags -> one host wait."""
+        s, t = self.shard, self.tr.torch
+        if self._flags_all is None:
+            self._flags_all = t.zeros(2 * self.world, dtype=t.int32, device=s.device)
+            self._flags_host = t.zeros(2 * self.world, dtype=t.int32).pin_memory()
+        with t.cuda.stream(s.stream):
+            send, recv = s.frozen_pack()
+            self.tr.sendrecv(send, recv, wait=False)
+            s.frozen_ghosts()
+            s.step_begin()
+            self.tr.dist.all_gather_into_tensor(self._flags_all, s.flags, group=self.tr.group)
+            self._flags_host.copy_(self._flags_all, non_blocking=True)
+        s.step_end()  # waits for the stream: the flags of all slabs are on the host as well
+        self.moved = False
+        return self._flags_host.numpy().reshape(self.world, 2).astype(np.float64)
+
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
-            self._exchange_halos()
-            n_div, want = self.shard.step_local()
-            self.iteration += 1
-            if not (self.can_divide or self.use_lists):
-                continue  # nothing to agree on: every step searches afresh
-            # one small all_gather per step: divisions need the lists of all slabs for the identifiers,
-            # and the persistent neighbour structure is rebuilt in all slabs at once
-            st = self.tr.allgather([n_div, int(want or self.moved)])
+            if STREAM_ORDERED and self.use_lists and not self.rebuild_next:
+                st = self._frozen_step()
+                self.iteration += 1
+            else:
+                self._exchange_halos()
+                n_div, want = self.shard.step_local()
+                self.iteration += 1
+                if not (self.can_divide or self.use_lists):
+                    continue  # nothing to agree on: every step searches afresh
+                # one small all_gather per step: divisions need the lists of all slabs for the
+                # identifiers, and the persistent neighbour structure is rebuilt in all slabs at once
+                st = self.tr.allgather([n_div, int(want or self.moved)])
             self.rebuild_next = bool(st[:, 1].max() > 0) or not self.use_lists
             if st[:, 0].sum() > 0:
                 gs, vx = self.shard.pending_divisions()

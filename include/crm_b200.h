@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CRM_ABI_VERSION 2
+#define CRM_ABI_VERSION 3
 
 typedef enum crm_status {
     CRM_OK = 0,
@@ -263,6 +263,23 @@ int crm_sim_pack_leavers(crm_sim* sim, void* dev_buf, uint32_t cap, uint32_t* n)
  * neighbours' record counts [2], flags [2] and the largest extent they reported. */
 int crm_sim_set_ghosts_msgs(crm_sim* sim, const void* dev_msg_lo, const void* dev_msg_hi, const void* dev_self,
                             uint32_t n_self, uint32_t* counts, uint32_t* flags, float* max_extent);
+/* Stream-ordered variants for the steps between two collective rebuilds (the reference's sub-domain
+ * threads exchange forces and positions through channels without a global barrier as well:
+ * cellular_raza chili run_main update_mechanics_interaction_step_1..3).  None of them waits for the
+ * device; the caller's transport must be ordered on crm_sim_stream (a cudaStream_t).
+ *   crm_sim_halo_repack     the frozen selections packed again into the two messages
+ *   crm_sim_ghosts_refresh  received records scattered to the ghost slots of the last rebuild step
+ *   crm_sim_step_begin      the step enqueued; dev_flags[0..1] = {divisions, reason to rebuild}
+ *                           written on the stream (device memory, may be NULL)
+ *   crm_sim_step_end        one stream synchronisation + the host part of the step
+ * crm_sim_step(sim, 1) == crm_sim_step_begin(sim, NULL) + crm_sim_step_end(sim). */
+void* crm_sim_stream(const crm_sim* sim);
+/* ... or make the sim run on a stream the caller owns (it must outlive the sim). */
+int crm_sim_set_stream(crm_sim* sim, void* stream);
+int crm_sim_halo_repack(crm_sim* sim, void* dev_msg_lo, void* dev_msg_hi);
+int crm_sim_ghosts_refresh(crm_sim* sim, const void* dev_msg_lo, const void* dev_msg_hi);
+int crm_sim_step_begin(crm_sim* sim, uint32_t* dev_flags);
+int crm_sim_step_end(crm_sim* sim);
 /* Migration (the reference re-sorts agents into voxels / sub-domains after every step): remove the
  * owned rods whose centroid left the slab and write their full records (device state, parameters,
  * identifier, parent, global slot) into HOST buffers; append received records as owned rods. */

@@ -24,7 +24,7 @@ def test_every_declared_symbol_is_exported():
     assert len(names) >= 25
     missing = [n for n in names if not hasattr(lib.lib, n)]
     assert not missing, missing
-    assert lib.fn("abi_version")() == 2
+    assert lib.fn("abi_version")() == 3
 
 
 def test_struct_layouts_match_header():
