@@ -245,7 +245,6 @@ class Shard:
         rebuild step on both ends)."""
         L, h = self.lib, self.sim.h
         L.check(L.fn("sim_halo_repack")(h, *self._msg_ptrs(self.send)))
-        L.fn("sim_keep_lists")(h)
         self.n_self = 0
         cut = lambda bufs, n: [b[:HEADER_BYTES + k * self.rb] if (side == 0 and self.rank > 0) or
                                (side == 1 and self.rank + 1 < self.partition.world) else b[:0]
@@ -254,6 +253,10 @@ class Shard:
 
     def frozen_ghosts(self):
         self.lib.check(self.lib.fn("sim_ghosts_refresh")(self.sim.h, *self._msg_ptrs(self.recv)))
+
+    def keep_lists(self):
+        """All slabs agreed after the last step that nothing moved far enough: reuse the structure."""
+        self.lib.fn("sim_keep_lists")(self.sim.h)
 
     def step_begin(self):
         """Enqueue the step; ``self.flags`` (device int32[2]) receives [divisions, reason to rebuild]."""
@@ -431,6 +434,7 @@ class LocalCluster:
         t.cuda.synchronize()
         for s in self.shards:
             s.frozen_ghosts()
+            s.keep_lists()
             s.step_begin()
         status = [s.step_end() for s in self.shards]
         for s, st in zip(self.shards, status):  # the device-written flags are what the ranks all_gather
@@ -563,6 +567,7 @@ class DistributedShard:
         self.coord = None
         self.emax_global = 0.0
         self._flags_all = self._flags_host = None
+        self._halo_ahead = False
 
     def close(self):
         self.shard.close()
@@ -609,15 +614,26 @@ class DistributedShard:
             self._flags_all = t.zeros(2 * self.world, dtype=t.int32, device=s.device)
             self._flags_host = t.zeros(2 * self.world, dtype=t.int32).pin_memory()
         with t.cuda.stream(s.stream):
-            send, recv = s.frozen_pack()
-            self.tr.sendrecv(send, recv, wait=False)
-            s.frozen_ghosts()
+            if not self._halo_ahead:
+                self._frozen_halo()
+            s.keep_lists()
             s.step_begin()
             self.tr.dist.all_gather_into_tensor(self._flags_all, s.flags, group=self.tr.group)
             self._flags_host.copy_(self._flags_all, non_blocking=True)
+            # the halo of the NEXT step, enqueued while this one runs: it is what the next step needs if
+            # no slab asks for a rebuild (the common case), and harmless otherwise (it only touches the
+            # exchange buffers and ghost slots, which a rebuild step fills again)
+            self._frozen_halo()
+            self._halo_ahead = True
         s.step_end()  # waits for the stream: the flags of all slabs are on the host as well
         self.moved = False
         return self._flags_host.numpy().reshape(self.world, 2).astype(np.float64)
+
+    def _frozen_halo(self):
+        s = self.shard
+        send, recv = s.frozen_pack()
+        self.tr.sendrecv(send, recv, wait=False)
+        s.frozen_ghosts()
 
     def step(self, n_steps: int = 1):
         for _ in range(n_steps):
@@ -625,6 +641,7 @@ class DistributedShard:
                 st = self._frozen_step()
                 self.iteration += 1
             else:
+                self._halo_ahead = False
                 self._exchange_halos()
                 n_div, want = self.shard.step_local()
                 self.iteration += 1
