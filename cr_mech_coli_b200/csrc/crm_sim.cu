@@ -34,7 +34,8 @@ static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st) 
 // grow every per-rod array to `need` slots, preserving the first s->n
 int crm_reserve(crm_sim* s, uint32_t need) {
     if (need <= s->cap) return 0;
-    uint32_t cap = s->cap ? s->cap : 1024;
+    // first allocation: what the caller asks for (set_agents adds head room for growth); later: doubling
+    uint32_t cap = s->cap ? s->cap : (need + 4095u) / 4096u * 4096u;
     while (cap < need) cap *= 2;
     const size_t st_ = (size_t)3 * s->lp;
     const size_t on = s->n, oc = (size_t)s->n * st_;
@@ -324,10 +325,16 @@ __global__ void k_status_flags(const Status* st, float skin, uint32_t host_want,
 
 // A step is enqueued (step_enqueue: nothing waits for the device unless a search needs fresh bounds)
 // and finished (step_finish: one stream synchronisation, then the host's bookkeeping).
+static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags);
 static int step_enqueue(crm_sim* s, uint32_t* dev_flags) {
     if (s->pending_div) return fail(CRM_ERR_INVALID, "divisions of the last step are pending (crm_sim_apply_divisions)");
     if (s->step_open) return fail(CRM_ERR_INVALID, "the last step was not finished (crm_sim_step_end)");
     s->step_open = true;
+    const int rc = step_enqueue_open(s, dev_flags);
+    if (rc) s->step_open = false;  // nothing to finish
+    return rc;
+}
+static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     if (s->n == 0) {
         s->iteration += 1;
         if (dev_flags) CK(cudaMemsetAsync(dev_flags, 0, 2 * sizeof(uint32_t), s->stream));
@@ -412,12 +419,8 @@ static int step_finish(crm_sim* s) {
 }
 
 static int step_once(crm_sim* s) {
-    int rc = step_enqueue(s, nullptr);
-    if (rc) {
-        s->step_open = false;
-        return rc;
-    }
-    return step_finish(s);
+    const int rc = step_enqueue(s, nullptr);
+    return rc ? rc : step_finish(s);
 }
 
 static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
@@ -588,7 +591,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->nv = (int)nv;
     s->lp = lanes_per_rod((int)nv);
     s->n = 0;
-    int rc = crm_reserve(s, std::max<uint32_t>(n + n / 2 + 16, 1024));
+    int rc = crm_reserve(s, std::max<uint32_t>(n + n / 4 + 16, 1024));
     if (rc) return rc;
     s->iteration = 0;
     s->snaps.clear();
@@ -724,9 +727,7 @@ int crm_sim_set_stream(crm_sim* s, void* stream) {
 int crm_sim_step_begin(crm_sim* s, uint32_t* dev_flags) {
     if (!s) return fail(CRM_ERR_INVALID, "null sim");
     CK(cudaSetDevice(s->device));
-    int rc = step_enqueue(s, dev_flags);
-    if (rc) s->step_open = false;
-    return rc;
+    return step_enqueue(s, dev_flags);
 }
 
 int crm_sim_step_end(crm_sim* s) {

@@ -220,3 +220,47 @@ def test_persistent_lists_overflow_falls_back(product_lib):
     assert np.abs(pg - po).max() < TRAJ_ATOL
     assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
     assert g.list_stats()["eval_steps"] == 0
+
+
+def test_step_begin_end_on_a_caller_stream(product_lib):
+    """crm_sim_step == crm_sim_step_begin + crm_sim_step_end, also on a stream the caller owns
+    (crm_sim_set_stream); the device-written flags are [divisions, rebuild wish] of that step."""
+    import ctypes as C
+
+    import torch
+
+    n = 800
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.05)
+    pos = lattice_colony(n, seed=4)
+    par = mie_params(n, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    vel = np.random.default_rng(8).normal(0, 0.3, pos.shape).astype(np.float32)
+    vel[:, :, 2] = 0
+    a = _capi.Sim(product_lib, cfg)
+    b = _capi.Sim(product_lib, cfg)
+    stream = torch.cuda.Stream()
+    product_lib.check(product_lib.fn("sim_set_stream")(b.h, C.c_void_p(stream.cuda_stream)))
+    assert int(product_lib.fn("sim_stream")(b.h)) == stream.cuda_stream
+    flags = torch.zeros(2, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    for s in (a, b):
+        s.set_agents(pos, vel, par)
+    wishes = 0
+    for _ in range(60):
+        a.step(1)
+        product_lib.check(product_lib.fn("sim_step_begin")(b.h, C.c_void_p(flags.data_ptr())))
+        # a second begin before the end is refused
+        assert product_lib.fn("sim_step_begin")(b.h, None) != 0
+        product_lib.check(product_lib.fn("sim_step_end")(b.h))
+        f = flags.tolist()
+        assert f[0] == 0
+        assert f[1] == int(product_lib.fn("sim_wants_rebuild")(b.h))
+        wishes += f[1]
+    assert 0 < wishes < 60  # some steps asked for a new search, most did not
+    pa, va = a.get_state()[:2]
+    pb, vb = b.get_state()[:2]
+    assert np.array_equal(pa, pb) and np.array_equal(va, vb)
+    assert a.list_stats() == b.list_stats()
+    a.close()
+    b.close()
