@@ -77,6 +77,7 @@ IDENT_DTYPE = np.dtype([("kind", "<i8"), ("voxel", "<u8"), ("counter", "<u8")])
 POT_MORSE, POT_MIE = 0, 1
 SETTER_NORMAL, SETTER_EXPLICIT = 0, 1
 ID_DIVISION, ID_INITIAL, ID_INSERTED = 0, 1, 2
+ERR_BOUNDARY, ERR_NUMERIC, ERR_DIVISION = -3, -4, -5  # crm_status values reported per simulation
 
 STATUS_NAMES = {
     -1: "InvalidArgument",
@@ -177,6 +178,9 @@ class Library:
             "sim_skin": (C.c_float, [vp]),
             "sim_pack_leavers": (C.c_int, [vp, vp, u32, P(u32)]),
             "sim_set_ghosts_msgs": (C.c_int, [vp, vp, vp, vp, u32, vp, vp, P(C.c_float)]),
+            "sim_isolate_sim_errors": (C.c_int, [vp, C.c_int]),
+            "sim_get_sim_status": (C.c_int, [vp, vp]),
+            "sim_run_costs": (C.c_int, [vp, vp, u32, u32, vp, vp, vp]),
             "sim_stream": (vp, [vp]),
             "sim_set_stream": (C.c_int, [vp, vp]),
             "sim_halo_repack": (C.c_int, [vp, vp, vp]),

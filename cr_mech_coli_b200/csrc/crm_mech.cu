@@ -222,6 +222,9 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const float nnb = cp.has_nr ? (float)d.nn[a] : 0.0f;
     float4 vb = make_float4(0.f, 0.f, 0.f, 0.f);
     if (d.vbuild) vb = d.vbuild[(size_t)a * LP + li];
+    const bool iso = d.sim_fail != nullptr;
+    const uint32_t sim_a = iso ? d.tile[a] : 0u;
+    const bool frozen = iso && d.sim_fail[sim_a] != 0;
     const float tension = mp.x, rigidity = mp.y, damping = mp.z, diffusion = mp.w;
     const float L = gs.z;
 
@@ -319,7 +322,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         rate = __fmul_rn(gs.x, powf(fmaxf(__fdiv_rn(__fsub_rn(mx, nnb), mx), 0.0f), cp.nr_exp));
     }
     const float newL = __fadd_rn(L, __fmul_rn(__fmul_rn(rate, dt), L));
-    const bool dividing = newL > gs.y;
+    bool dividing = newL > gs.y && !frozen;
 
     bool inside = true;
     if (!dividing) {  // dividing rods are reflected after the division (k_divide)
@@ -328,7 +331,18 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         inside &= reflect(Pnew[2], Vnew[2], d.lz);
     }
     const bool finite = isfinite(Pnew[0]) && isfinite(Pnew[1]) && isfinite(Pnew[2]);
-    if (hv) {
+    bool keep = false;  // isolation: this rod keeps its old state
+    if (iso) {
+        const unsigned bad = __ballot_sync(gm, hv && (!finite || !inside)) & group_mask<LP>();
+        if (bad && l == 0 && valid && !frozen) d.sim_fail[sim_a] = (bad && !finite) ? CRM_ERR_NUMERIC : CRM_ERR_BOUNDARY;
+        keep = bad != 0 || frozen;
+        if (keep) {
+            dividing = false;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) Pnew[c] = P[c];
+        }
+    }
+    if (hv && !keep) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             d.pos[o + c * LP + l] = Pnew[c];
@@ -377,7 +391,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             }
         }
     }
-    if (l == 0 && valid) {
+    if (l == 0 && valid && !keep) {
         gs.z = newL;
         d.grow[a] = gs;
         if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
@@ -482,8 +496,19 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
             d.vel[ob + c * LP + l] = V2[c];
         }
         if (!finite || !inside) {
-            if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
+            if (d.sim_fail) {  // isolation: flag the sim, park the daughters inside the domain
+                d.sim_fail[d.tile[a]] = finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC;
+                const float hi[3] = {d.lx, d.ly, d.lz};
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    D1[c] = fminf(fmaxf(isfinite(D1[c]) ? D1[c] : 0.5f * hi[c], 0.0f), hi[c]);
+                    D2[c] = fminf(fmaxf(isfinite(D2[c]) ? D2[c] : 0.5f * hi[c], 0.0f), hi[c]);
+                    d.pos[oa + c * LP + l] = D1[c];
+                    d.pos[ob + c * LP + l] = D2[c];
+                }
+            } else if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0) {
                 d.status->err_slot = a;
+            }
         }
     }
     // the new cell starts with an empty increment history

@@ -550,7 +550,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -606,6 +606,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->sim_rods.clear();
     s->n_sims = 1;
     s->d.tile = nullptr;
+    s->d.sim_fail = nullptr;
     s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1], 0);
     std::vector<PotParams> pot(n);
     std::vector<MechParams> mech(n);
@@ -673,6 +674,8 @@ int crm_sim_set_agents_batched(crm_sim* s, const float* pos, const float* vel, c
     s->n_sims = n_sims;
     s->sim_of.assign(sim_of, sim_of + n);
     s->sim_rods.assign(n_sims, 0);
+    s->sim_rods0.assign(n_sims, 0);
+    for (uint32_t a = 0; a < n; ++a) s->sim_rods0[sim_of[a]]++;
     s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1] * n_sims, 0);
     for (uint32_t a = 0; a < n; ++a) {  // Initial(index inside the own sim)
         const uint64_t k = s->sim_rods[sim_of[a]]++;
@@ -682,6 +685,124 @@ int crm_sim_set_agents_batched(crm_sim* s, const float* pos, const float* vel, c
     if (n) CK(cudaMemcpyAsync(s->tile_buf, sim_of, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     s->d.tile = s->tile_buf;
+    return 0;
+}
+
+// Error isolation of batched sims: a BoundaryError / CalcError stops only the sim it happens in
+// (the reference evaluates every parameter point in its own run and maps an error to the error cost of
+// that member alone, src/crm_fit/predict.rs:224-228,249-256).
+int crm_sim_isolate_sim_errors(crm_sim* s, int on) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    if (s->sim_of.empty()) return fail(CRM_ERR_INVALID, "not a batched sim (crm_sim_set_agents_batched)");
+    CK(cudaSetDevice(s->device));
+    if (on) {
+        if (s->sim_fail) CK(cudaFree(s->sim_fail));
+        CK(cudaMalloc(&s->sim_fail, sizeof(int) * s->n_sims));
+        CK(cudaMemsetAsync(s->sim_fail, 0, sizeof(int) * s->n_sims, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    s->d.sim_fail = on ? s->sim_fail : nullptr;
+    return 0;
+}
+
+// Per sim: 0 | CRM_ERR_BOUNDARY | CRM_ERR_NUMERIC (isolated errors) | CRM_ERR_DIVISION (the sim has
+// divided; only reported, divisions are legal outside the cost evaluation).
+int crm_sim_get_sim_status(crm_sim* s, int32_t* out) {
+    if (!s || !out) return fail(CRM_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    for (uint32_t m = 0; m < s->n_sims; ++m) out[m] = 0;
+    if (s->d.sim_fail) {
+        CK(cudaMemcpyAsync(out, s->sim_fail, sizeof(int) * s->n_sims, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    for (uint32_t m = 0; m < s->n_sims && m < s->sim_rods0.size(); ++m)
+        if (out[m] == 0 && s->sim_rods[m] != s->sim_rods0[m]) out[m] = CRM_ERR_DIVISION;
+    return 0;
+}
+
+// ---- cost of a batched ensemble, reduced on the device -------------------------------------------
+// One block per sim, fixed-order tree: cost[m] += sum over the sim's rods and vertices of the squared xy
+// distance to targets[r][rod index inside the sim][vertex][0..1] (reference src/crm_fit/predict.rs:258-285).
+__global__ void __launch_bounds__(128) k_cost(const float* __restrict__ pos, int nv, int lp, const uint32_t* __restrict__ start,
+                                              const float* __restrict__ target, uint32_t n_agents, float* __restrict__ cost) {
+    __shared__ float red[128];
+    const uint32_t m = blockIdx.x;
+    const uint32_t s0 = start[m], s1 = start[m + 1];
+    float acc = 0.0f;
+    for (uint32_t i = s0 * nv + threadIdx.x; i < s1 * nv; i += 128) {
+        const uint32_t rod = i / nv, v = i % nv;
+        const float x = pos[(size_t)rod * 3 * lp + v], y = pos[(size_t)rod * 3 * lp + lp + v];
+        const float* t = target + ((size_t)(rod - s0) * nv + v) * 2;
+        const float dx = x - t[0], dy = y - t[1];
+        acc += dx * dx + dy * dy;
+    }
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) cost[m] += red[0];
+    (void)n_agents;
+}
+
+// Steps to t_max without snapshots and accumulates, at the given iterations, every sim's cost against
+// targets[n_results][n_agents][n_vertices][2] (host, f32).  Errors are isolated per sim; out_status as
+// crm_sim_get_sim_status.  Rods must be grouped by sim in the order of set_agents_batched.
+int crm_sim_run_costs(crm_sim* s, const float* targets, uint32_t n_results, uint32_t n_agents,
+                      const uint64_t* result_iterations, float* out_costs, int32_t* out_status) {
+    if (!s || !targets || !result_iterations || !out_costs) return fail(CRM_ERR_INVALID, "null argument");
+    if (s->sim_of.empty()) return fail(CRM_ERR_INVALID, "not a batched sim (crm_sim_set_agents_batched)");
+    CK(cudaSetDevice(s->device));
+    std::vector<uint32_t> start(s->n_sims + 1, 0);
+    for (uint32_t a = 0; a < s->n; ++a) {
+        if (a && s->sim_of[a] < s->sim_of[a - 1]) return fail(CRM_ERR_INVALID, "rods are not grouped by sim");
+        start[s->sim_of[a] + 1]++;
+    }
+    for (uint32_t m = 0; m < s->n_sims; ++m) {
+        if (start[m + 1] > n_agents) return fail(CRM_ERR_INVALID, "sim %u has %u rods, the data %u", m, start[m + 1], n_agents);
+        start[m + 1] += start[m];
+    }
+    for (uint32_t r = 1; r < n_results; ++r)
+        if (result_iterations[r] <= result_iterations[r - 1]) return fail(CRM_ERR_INVALID, "result iterations must increase");
+    int rc = crm_sim_isolate_sim_errors(s, 1);
+    if (rc) return rc;
+    float *d_target = nullptr, *d_cost = nullptr;
+    uint32_t* d_start = nullptr;
+    const size_t per_result = (size_t)n_agents * s->nv * 2;
+    auto cleanup = [&]() {
+        cudaFree(d_target);
+        cudaFree(d_cost);
+        cudaFree(d_start);
+    };
+    CK(cudaMalloc(&d_target, sizeof(float) * per_result * std::max(1u, n_results)));
+    CK(cudaMalloc(&d_cost, sizeof(float) * s->n_sims));
+    CK(cudaMalloc(&d_start, sizeof(uint32_t) * (s->n_sims + 1)));
+    cudaMemcpyAsync(d_target, targets, sizeof(float) * per_result * n_results, cudaMemcpyHostToDevice, s->stream);
+    cudaMemcpyAsync(d_start, start.data(), sizeof(uint32_t) * (s->n_sims + 1), cudaMemcpyHostToDevice, s->stream);
+    cudaMemsetAsync(d_cost, 0, sizeof(float) * s->n_sims, s->stream);
+    uint32_t next = 0;
+    auto accumulate = [&]() {
+        while (next < n_results && result_iterations[next] < s->iteration) next++;
+        if (next < n_results && result_iterations[next] == s->iteration) {
+            k_cost<<<s->n_sims, 128, 0, s->stream>>>(s->d.pos, s->nv, s->lp, d_start, d_target + per_result * next, n_agents, d_cost);
+            s->launches += 1;
+            next++;
+        }
+    };
+    accumulate();
+    while (s->iteration < s->max_iter) {  // to t_max like the reference: a late error still costs the member
+        if ((rc = step_once(s))) {
+            cleanup();
+            return rc;
+        }
+        accumulate();
+    }
+    cudaMemcpyAsync(out_costs, d_cost, sizeof(float) * s->n_sims, cudaMemcpyDeviceToHost, s->stream);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(CRM_ERR_CUDA, "cost evaluation: %s", cudaGetErrorString(e));
+    if (out_status && (rc = crm_sim_get_sim_status(s, out_status))) return rc;
     return 0;
 }
 

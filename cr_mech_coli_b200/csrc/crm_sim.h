@@ -87,6 +87,8 @@ struct crm_sim {
     uint32_t n_sims = 1;
     uint32_t* tile_buf = nullptr;        // device copy of sim_of (Dev::tile points here when batched)
     std::vector<uint64_t> sim_rods;      // batched sims: rods ever created per sim (next local slot)
+    std::vector<uint32_t> sim_rods0;     // batched sims: rods at set_agents (a sim that divided has more now)
+    int* sim_fail = nullptr;             // device [n_sims], Dev::sim_fail points here while isolation is on
     std::vector<crm::DivRecord> h_div;
     uint64_t iteration = 0, rod_steps = 0, launches = 0;
     std::vector<uint64_t> save_iter;

@@ -153,6 +153,19 @@ int crm_sim_set_agents(crm_sim* sim, const float* pos, const float* vel,
 int crm_sim_set_agents_batched(crm_sim* sim, const float* pos, const float* vel, const crm_rod_params* params,
                                const uint32_t* sim_of, uint32_t n_rods, uint32_t n_vertices, uint32_t n_sims);
 int crm_sim_get_sim_index(const crm_sim* sim, uint32_t* out);
+/* Error isolation: a BoundaryError / CalcError stops only the simulation it happens in (its rods keep
+ * their last valid state), like the reference's one run per parameter point where an error costs that
+ * member alone (src/crm_fit/predict.rs:224-228,249-256).  Status per simulation: 0, CRM_ERR_BOUNDARY,
+ * CRM_ERR_NUMERIC, or CRM_ERR_DIVISION if the simulation has divided (reported, not an error). */
+int crm_sim_isolate_sim_errors(crm_sim* sim, int on);
+int crm_sim_get_sim_status(crm_sim* sim, int32_t* out);
+/* `predict_calculate_cost_rs` for a whole population (reference src/crm_fit/predict.rs:231-287): steps
+ * to the last result iteration without snapshots and accumulates on the device, at result_iterations[r]
+ * (increasing), every simulation's sum of squared xy distances to targets[r][rod][vertex][0..1]
+ * (host f32 [n_results][n_agents][n_vertices][2]; rod = index inside its simulation).  Errors are
+ * isolated; out_status as crm_sim_get_sim_status (may be NULL). */
+int crm_sim_run_costs(crm_sim* sim, const float* targets, uint32_t n_results, uint32_t n_agents,
+                      const uint64_t* result_iterations, float* out_costs, int32_t* out_status);
 int crm_sim_snapshot_sim_index(const crm_sim* sim, uint32_t k, uint32_t* out);
 
 /* The whole of `run_main!` (reference src/simulation.rs:283-292): steps to
