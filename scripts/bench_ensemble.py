@@ -16,6 +16,8 @@ ap.add_argument("--sims", type=int, default=512)
 ap.add_argument("--rods", type=int, default=64)
 ap.add_argument("--steps", type=int, default=200)
 ap.add_argument("--cpu-sims", type=int, default=4)
+ap.add_argument("--full-cost", action="store_true",
+                help="also time one whole population cost evaluation (t_max 17.5, dt 0.002 = 8750 steps, device-side costs)")
 args = ap.parse_args()
 lib = _capi.product()
 cfg = _capi.make_config(domain_size=(200.0, 200.0), n_voxels=(1, 1), dt=0.002, t_max=1e6, n_saves=0)
@@ -46,4 +48,14 @@ if args.cpu_sims:
         o.step(args.steps)
     dt = time.perf_counter() - t0
     out["cpu_oracle_sim_steps_per_s_1core"] = args.cpu_sims * args.steps / dt
+g.close()
+if args.full_cost:
+    from cr_mech_coli_b200.crm_fit import costs_on_device
+    cfg2 = _capi.make_config(domain_size=(200.0, 200.0), n_voxels=(1, 1), dt=0.002, t_max=17.5, n_saves=8)
+    data = np.repeat(pos[0][None, :, :, :2], 3, axis=0).astype(np.float32)
+    t0 = time.perf_counter()
+    costs, status = costs_on_device(lib, cfg2, P, np.zeros_like(P), Q, S, args.sims, data, [3, 6, 9])
+    dt = time.perf_counter() - t0
+    out["population_cost_eval"] = {"seconds": dt, "steps": 8750, "members": args.sims, "failed_members": int((status != 0).sum()),
+                                   "members_per_s": args.sims / dt, "finite": bool(np.isfinite(costs).all())}
 print(json.dumps(out))
