@@ -181,6 +181,9 @@ class Library:
             "sim_isolate_sim_errors": (C.c_int, [vp, C.c_int]),
             "sim_get_sim_status": (C.c_int, [vp, vp]),
             "sim_run_costs": (C.c_int, [vp, vp, u32, u32, vp, vp, vp]),
+            "sim_patch_count": (C.c_uint64, [vp]),
+            "sim_last_forces": (C.c_int, [vp, vp]),
+            "sim_set_patching": (C.c_int, [vp, C.c_int]),
             "sim_stream": (vp, [vp]),
             "sim_set_stream": (C.c_int, [vp, vp]),
             "sim_halo_repack": (C.c_int, [vp, vp, vp]),
@@ -321,6 +324,15 @@ class Sim:
         b, e = C.c_uint64(0), C.c_uint64(0)
         self.L.check(self.L.fn("sim_list_stats")(self.h, C.byref(b), C.byref(e)))
         return {"builds": int(b.value), "eval_steps": int(e.value)}
+
+    def last_forces(self):
+        f = np.zeros((self.n_rods, self.n_vertices, 3), dtype=np.float32)
+        self.L.check(self.L.fn("sim_last_forces")(self.h, _fptr(f)))
+        return f
+
+    def patch_count(self) -> int:
+        """Division steps absorbed by patching the live neighbour structure (no new search)."""
+        return int(self.L.fn("sim_patch_count")(self.h))
 
     def compute_forces(self):
         n, nv = self.n_rods, self.n_vertices

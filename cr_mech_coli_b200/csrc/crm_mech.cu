@@ -163,6 +163,7 @@ __global__ void k_bin_sort(Dev d, uint32_t ncells) {
     }
     for (uint32_t i = s; i < e; ++i) {  // cell-sorted copies of the bounds for the force kernel's candidate scan
         const uint32_t v = d.sorted[i];
+        d.gof[v] = i;
         d.bs_sorted[i] = d.bsphere[v];
         d.chord_sorted[2 * i] = d.chord[2 * v];
         d.chord_sorted[2 * i + 1] = d.chord[2 * v + 1];
@@ -357,7 +358,12 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     }
     if (d.vbuild) {  // displacement since the persistent neighbour structure was built
         const float ex = Pnew[0] - vb.x, ey = Pnew[1] - vb.y, ez = Pnew[2] - vb.z;
-        const float dd = group_max<LP>(hv ? ex * ex + ey * ey + ez * ez : 0.0f, gm);
+        float e2 = ex * ex + ey * ey + ez * ez;
+        if (vb.w > 0.0f) {  // a daughter: part of the budget was used up before its division
+            const float e = sqrtf(e2) + vb.w;
+            e2 = e * e;
+        }
+        const float dd = group_max<LP>(hv ? e2 : 0.0f, gm);
         if (l == 0 && valid) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
     }
     // The bounds of the search (sphere, chord, cull thresholds) are recomputed by k_bounds only when a
@@ -483,9 +489,35 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
         D2[2] = z0 * (1.0f - p) + z1 * p;
     }
     float V1[3] = {V[0], V[1], V[2]}, V2[3] = {V[0], V[1], V[2]};
+    const float U1[3] = {D1[0], D1[1], D1[2]}, U2[3] = {D2[0], D2[1], D2[2]};  // before the reflection
     bool inside = true;
     inside &= reflect(D1[0], V1[0], d.lx); inside &= reflect(D1[1], V1[1], d.ly); inside &= reflect(D1[2], V1[2], d.lz);
     inside &= reflect(D2[0], V2[0], d.lx); inside &= reflect(D2[1], V2[1], d.ly); inside &= reflect(D2[2], V2[2], d.lz);
+    // Budget of the persistent neighbour structure the daughters start with: they lie on the mother's
+    // polyline, so whatever is out of the mother's reach is out of theirs, up to (i) the mother's own
+    // displacement since the structure was built, (ii) the corner a daughter segment cuts where it spans a
+    // mother vertex, (iii) a reflection at the boundary.  The sum goes into vbuild.w (k_integrate adds it).
+    float slack = 0.0f;
+    if (d.vbuild) {
+        const float4 vbm = d.vbuild[(size_t)a * LP + li];
+        const float mx = P[0] - vbm.x, my = P[1] - vbm.y, mz = P[2] - vbm.z;
+        float far = hv ? sqrtf(mx * mx + my * my + mz * mz) : 0.0f;
+        const float r1x = D1[0] - U1[0], r1y = D1[1] - U1[1], r1z = D1[2] - U1[2];
+        const float r2x = D2[0] - U2[0], r2y = D2[1] - U2[1], r2z = D2[2] - U2[2];
+        float refl = hv ? fmaxf(sqrtf(r1x * r1x + r1y * r1y + r1z * r1z), sqrtf(r2x * r2x + r2y * r2y + r2z * r2z)) : 0.0f;
+        far = group_max<LP>(far, gm);
+        refl = group_max<LP>(refl, gm);
+        float sag = 0.0f;
+#pragma unroll
+        for (int q = 1; q < NV - 1; ++q) {  // distance of mother vertex q from the chord of its neighbours
+            const float cx = X[q + 1] - X[q - 1], cy = Y[q + 1] - Y[q - 1], cz = Z[q + 1] - Z[q - 1];
+            const float wx = X[q] - X[q - 1], wy = Y[q] - Y[q - 1], wz = Z[q] - Z[q - 1];
+            const float kx = wy * cz - wz * cy, ky = wz * cx - wx * cz, kz = wx * cy - wy * cx;
+            const float c2 = cx * cx + cy * cy + cz * cz;
+            sag = fmaxf(sag, c2 > 0.0f ? sqrtf((kx * kx + ky * ky + kz * kz) / c2) : sqrtf(wx * wx + wy * wy + wz * wz));
+        }
+        slack = (far + fmaxf(vbm.w, 0.0f) + sag + refl) * 1.0001f + 1e-6f;
+    }
     const bool finite = isfinite(D1[0]) && isfinite(D1[1]) && isfinite(D1[2]) && isfinite(D2[0]) && isfinite(D2[1]) && isfinite(D2[2]);
     if (hv) {
 #pragma unroll
@@ -510,6 +542,10 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
                 d.status->err_slot = a;
             }
         }
+    }
+    if (d.vbuild) {
+        d.vbuild[(size_t)a * LP + l] = make_float4(D1[0], D1[1], D1[2], slack);
+        d.vbuild[(size_t)b * LP + l] = make_float4(D2[0], D2[1], D2[2], slack);
     }
     // the new cell starts with an empty increment history
     {
@@ -591,6 +627,52 @@ void launch_integrate(int nv, const Dev& d, cudaStream_t st) {
     CRM_NV_LIST(X)
 #undef X
 }
+// ------------------------------------------------------------------------------------
+// Divisions while the persistent neighbour structure is live.  Phase 1 (one thread per division): the new
+// daughter gets a row of its own, a copy of the mother's list; the two daughters become each other's extra
+// candidates.  Phase 2 (one thread per (division, listed neighbour)): every rod that lists the mother gets
+// the new daughter as an extra candidate, and so does the daughter such a rod split off in the same step.
+// All those rows are queued in dirty_list for k_force<.., LISTS>.
+__device__ __forceinline__ void patch_add(const Dev& d, uint32_t g, uint32_t slot, int lp, int maxp) {
+    const uint32_t p = atomicAdd(&d.dcnt[g], 1u);
+    if (p < PATCH_EXTRA) d.dextra[(size_t)g * PATCH_EXTRA + p] = slot;
+    // the rebuilt row keeps every candidate: it has to fit (the list step after this one reads it)
+    if (p >= PATCH_EXTRA || (d.pnq[(size_t)g * lp] >> 24) + p + 1 > (uint32_t)maxp) d.status->patch_overflow = 1u;
+    if (atomicExch(&d.dmark[g], 1u) == 0u) d.dirty_list[atomicAdd(d.dirty_n, 1u)] = g;
+}
+__global__ void k_patch_rows(Dev d, uint32_t n_div, uint32_t n0, int lp, int maxp) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_div) return;
+    const uint32_t a = d.divlist[r].slot, b = n0 + r;
+    const uint32_t ga = d.gof[a], gb = n0 + r;  // rows and slots are both appended in division order
+    d.sorted[gb] = b;
+    d.gof[b] = gb;
+    const uint32_t cnt = d.pnq[(size_t)ga * lp] >> 24;
+    for (uint32_t i = 0; i < cnt; ++i) d.plist[(size_t)gb * maxp + i] = d.plist[(size_t)ga * maxp + i];
+    for (int l = 0; l < lp; ++l) d.pnq[(size_t)gb * lp + l] = cnt << 24;
+    d.dsib[ga] = gb;
+    patch_add(d, ga, b, lp, maxp);
+    patch_add(d, gb, a, lp, maxp);
+}
+__global__ void k_patch_neighbours(Dev d, uint32_t n_div, uint32_t n0, int lp, int maxp) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t r = t / maxp, i = t % maxp;
+    if (r >= n_div) return;
+    const uint32_t a = d.divlist[r].slot, b = n0 + r;
+    const uint32_t ga = d.gof[a];
+    if (i >= (d.pnq[(size_t)ga * lp] >> 24)) return;
+    const uint32_t gc = d.gof[d.plist[(size_t)ga * maxp + i]];
+    patch_add(d, gc, b, lp, maxp);
+    const uint32_t gs = d.dsib[gc];
+    if (gs != 0xffffffffu) patch_add(d, gs, b, lp, maxp);
+}
+int launch_patch(const Dev& d, uint32_t n_div, uint32_t n0, int lp, int maxp, cudaStream_t st) {
+    if (n_div == 0) return 0;
+    k_patch_rows<<<blocks_for(n_div, 128), 128, 0, st>>>(d, n_div, n0, lp, maxp);
+    k_patch_neighbours<<<blocks_for((uint64_t)n_div * maxp, 128), 128, 0, st>>>(d, n_div, n0, lp, maxp);
+    return 2;
+}
+
 void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st) {
     if (n_div == 0) return;
 #define X(NVV) if (nv == NVV) k_divide<NVV><<<blocks_for((uint64_t)n_div * Lay<NVV>::LP, 128), 128, 0, st>>>(d, n_div, n0);

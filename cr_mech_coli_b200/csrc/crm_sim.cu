@@ -64,6 +64,16 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.pqs, 0, (size_t)cap * PL_QS * s->lp);
     G(s->d.pnq, 0, (size_t)cap * s->lp);
     G(s->d.vbuild, 0, (size_t)cap * s->lp);
+    G(s->d.gof, 0, (size_t)cap);
+    G(s->d.dcnt, 0, (size_t)cap);
+    G(s->d.dextra, 0, (size_t)cap * PATCH_EXTRA);
+    G(s->d.dmark, 0, (size_t)cap);
+    G(s->d.dsib, 0, (size_t)cap);
+    G(s->d.dirty_list, 0, (size_t)cap);
+    CK(cudaMemsetAsync(s->d.dsib, 0xff, sizeof(uint32_t) * cap, s->stream));
+    if (!s->d.dirty_n) CK(cudaMalloc(&s->d.dirty_n, sizeof(uint32_t)));
+    CK(cudaMemsetAsync(s->d.dirty_n, 0, sizeof(uint32_t), s->stream));
+    s->n_dirty = 0;
     s->need_rebuild = true;  // the structure does not survive a reallocation
     s->have_lists = false;
     G(s->d.cell_of, 0, (size_t)cap);
@@ -211,11 +221,34 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     int rc = crm_reserve(s, n0 + n_div);
     if (rc) return rc;
     CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     launch_divide(s->nv, s->d, n_div, n0, s->stream);
     s->launches += 1;
+    // Divisions were the only reason to search again and the structure is live: patch it (the rows of the
+    // daughters and of the mothers' neighbours are rebuilt from candidate lists at the start of the next step)
+    const bool patch = s->patch_divisions && s->have_lists && !s->need_rebuild && !s->sharded && s->skin > 0.0f;
+    s->patch_divisions = false;
+    uint32_t* const h_dirty = reinterpret_cast<uint32_t*>(s->h_status + 1) + 16;  // pinned scratch behind the status
+    if (patch) {
+        CK(cudaMemsetAsync(s->d.dirty_n, 0, sizeof(uint32_t), s->stream));
+        s->launches += launch_patch(s->d, n_div, n0, s->lp, s->lp > 8 ? 8 : 16, s->stream);
+        CK(cudaMemcpyAsync(h_dirty, s->d.dirty_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    }
     CK(cudaGetLastError());
     if ((rc = crm_read_status(s))) return rc;
     if ((rc = crm_report_device_error(s))) return rc;
+    bool patched = false;
+    if (patch) {
+        patched = s->h_status->patch_overflow == 0;
+        if (patched) {
+            s->n_dirty = *h_dirty;
+            s->n_patches += 1;
+        } else {  // a row ran out of room for the announced rods: search again, scratch arrays back to empty
+            CK(cudaMemsetAsync(s->d.dcnt, 0, sizeof(uint32_t) * s->cap, s->stream));
+            CK(cudaMemsetAsync(s->d.dmark, 0, sizeof(uint32_t) * s->cap, s->stream));
+            CK(cudaMemsetAsync(s->d.dsib, 0xff, sizeof(uint32_t) * s->cap, s->stream));
+        }
+    }
     s->base.resize(n0 + n_div);
     s->ids.resize(n0 + n_div);
     s->parents.resize(n0 + n_div);
@@ -237,8 +270,11 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     s->bounds_fresh = false;
     s->h_div.clear();
     s->pending_div = 0;
-    s->need_rebuild = true;
-    s->have_lists = false;
+    if (!patched) {
+        s->need_rebuild = true;
+        s->have_lists = false;
+        s->n_dirty = 0;
+    }
     return 0;
 }
 
@@ -306,6 +342,16 @@ static int launch_force_from_lists(crm_sim* s) {
     s->d.n = s->n + s->n_ghost;  // the build order covers the ghosts as well
     s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    if (s->n_dirty) {  // rows touched by the divisions of the last step: rebuilt with twice the skin as
+        // margin, because their partners' displacement budgets keep counting from the last full build
+        Dev dl = s->d;
+        dl.n_dirty = s->n_dirty;
+        dl.rsearch = s->rsearch + 2.0f * s->skin;
+        dl.skin = 2.0f * s->skin;
+        launch_force_lists(s->nv, dl, s->fast_math, s->stream);
+        s->launches += 1;
+        s->n_dirty = 0;
+    }
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
     launch_force_eval(s->nv, s->d, s->fast_math, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
@@ -348,18 +394,27 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     if (use_lists) {
         rc = launch_force_from_lists(s);
         s->n_eval_steps += 1;
+        s->evals_since_build += 1;
     } else {
         const bool build = persistent(s) && s->holdoff == 0;
         rc = launch_neighbour_and_force(s, false, build);
         if (build) {
-            // lists that repeatedly do not last (dividing colonies): stop writing them for a while
-            s->short_builds = (s->steps_since_build < 3 && s->n_builds > 0) ? s->short_builds + 1 : 0;
+            // lists that repeatedly are not used (a colony with divisions in every step): stop writing them
+            // for a while, twice as long every time it happens again (8 .. 512 steps)
+            if (s->evals_since_build >= 2 || s->n_builds == 0) {
+                s->short_builds = 0;
+                if (s->evals_since_build >= 2) s->backoff = 8;
+            } else {
+                s->short_builds += 1;
+            }
             if (s->short_builds >= 4) {
-                s->holdoff = 8;
+                s->holdoff = s->backoff;
+                s->backoff = std::min<uint32_t>(s->backoff * 2, 512);
                 s->short_builds = 0;
             }
             s->n_builds += 1;
             s->steps_since_build = 0;
+            s->evals_since_build = 0;
             s->need_rebuild = false;
             s->have_lists = true;
         } else {
@@ -395,15 +450,20 @@ static int step_finish(crm_sim* s) {
     }
     if ((rc = crm_report_device_error(s))) return rc;
     const uint32_t n_div = s->h_status->n_div;
-    bool want = n_div > 0 || s->h_status->n_leave > 0;
+    bool want = s->h_status->n_leave > 0;
     if (persistent(s)) {
         if (s->h_status->plist_overflow) {  // a rod did not fit: search every step for a while, then retry
             s->have_lists = false;
             s->holdoff = 64;
         }
+        if (s->h_status->patch_overflow) want = true;  // a patched row is full: a fresh search empties it
         const float disp = std::sqrt(__builtin_bit_cast(float, s->h_status->disp2_bits));
         if (!(disp < 0.4999f * s->skin)) want = true;
     }
+    // divisions alone do not force a new search while the structure is live: its rows are patched
+    s->patch_divisions = n_div > 0 && !want && persistent(s) && s->have_lists && !s->need_rebuild && !s->sharded &&
+                         s->patching;
+    if (n_div > 0 && !s->patch_divisions) want = true;
     s->want_rebuild = want || !s->have_lists;
     // sharded runs rebuild in all slabs at once: the coordinator clears the flag (crm_sim_keep_lists)
     if (s->sharded || s->want_rebuild) s->need_rebuild = true;
@@ -521,10 +581,11 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     const char* ex = getenv("CRM_B200_EXACT_MATH");
     s->fast_math = !(ex && ex[0] == '1');
     if (const char* sk = getenv("CRM_B200_SKIN")) s->skin = std::max(0.0f, (float)atof(sk));
+    if (const char* pt = getenv("CRM_B200_PATCH")) s->patching = pt[0] != '0';
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaMalloc(&s->d.status, sizeof(Status)));
     CK(cudaMemset(s->d.status, 0, sizeof(Status)));
-    CK(cudaMallocHost(&s->h_status, sizeof(Status) + 64));  // + pinned scratch (message headers)
+    CK(cudaMallocHost(&s->h_status, sizeof(Status) + 128));  // + pinned scratch (message headers)
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
     s->d.lx = c->domain_size[0];
@@ -549,7 +610,7 @@ void crm_sim_destroy(crm_sim* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
-                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.cell_of, s->d.cell_rank,
+                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.gof, s->d.dcnt, s->d.dextra, s->d.dmark, s->d.dsib, s->d.dirty_list, s->d.dirty_n, s->d.cell_of, s->d.cell_rank,
                     s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -574,6 +635,14 @@ int crm_sim_set_skin(crm_sim* s, float skin) {
 int crm_sim_list_stats(const crm_sim* s, uint64_t* n_builds, uint64_t* n_eval_steps) {
     if (n_builds) *n_builds = s->n_builds;
     if (n_eval_steps) *n_eval_steps = s->n_eval_steps;
+    return 0;
+}
+
+// Divisions absorbed by patching the live structure (no new search), and the switch for it.
+uint64_t crm_sim_patch_count(const crm_sim* s) { return s ? s->n_patches : 0; }
+int crm_sim_set_patching(crm_sim* s, int on) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    s->patching = on != 0;
     return 0;
 }
 
@@ -631,6 +700,8 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->need_rebuild = true;
     s->have_lists = false;
     s->holdoff = 0;
+    s->backoff = 8;
+    s->evals_since_build = 0;
     s->steps_since_build = 0;
     const size_t m = (size_t)n * nv * 3;
     if (n) {
@@ -934,6 +1005,17 @@ int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
         CK(cudaMemcpyAsync(out_force, s->stage, sizeof(float) * (size_t)s->n * s->nv * 3, cudaMemcpyDeviceToHost, s->stream));
     }
     if (out_nn) CK(cudaMemcpyAsync(out_nn, s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    return 0;
+}
+
+// Interaction forces the last step used ([n][n_vertices][3]); tests compare them with a fresh search.
+int crm_sim_last_forces(crm_sim* s, float* out_force) {
+    if (!s || !out_force) return fail(CRM_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    if (s->n == 0) return 0;
+    launch_pack(s->nv, s->d.force, s->stage, s->n, s->stream);
+    CK(cudaMemcpyAsync(out_force, s->stage, sizeof(float) * (size_t)s->n * s->nv * 3, cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     return 0;
 }

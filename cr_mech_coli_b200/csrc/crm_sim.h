@@ -22,6 +22,8 @@ void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
 int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st);
 void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
 void launch_force_eval(int nv, const Dev& d, bool fast, cudaStream_t st);
+void launch_force_lists(int nv, const Dev& d, bool fast, cudaStream_t st);
+int launch_patch(const Dev& d, uint32_t n_div, uint32_t n0, int lp, int maxp, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
 void launch_divide(int nv, const Dev& d, uint32_t n_div, uint32_t n0, cudaStream_t st);
 // host helpers (crm_host.cpp)
@@ -76,7 +78,13 @@ struct crm_sim {
     uint32_t halo_sel_cap = 0;
     uint32_t holdoff = 0;       // steps for which rebuilding is not attempted (overflow / frequent rebuilds)
     uint32_t steps_since_build = 0;
-    uint32_t short_builds = 0;  // consecutive rebuilds that lasted fewer than 3 steps
+    uint32_t short_builds = 0;  // consecutive rebuilds whose lists served fewer than 2 steps
+    uint32_t evals_since_build = 0;
+    uint32_t n_dirty = 0;       // rows queued for k_force<LISTS> before the next list step (divisions)
+    uint32_t n_patches = 0;     // division steps absorbed without a new search
+    bool patching = true;       // CRM_B200_PATCH=0 / crm_sim_set_patching: search again after every division
+    bool patch_divisions = false;  // set by the step that saw divisions and no other reason to search again
+    uint32_t backoff = 8;       // next holdoff (doubles while the lists keep being useless)
     uint64_t n_builds = 0, n_eval_steps = 0;
     // host-side bookkeeping
     std::vector<crm_rod_params> base;  // cold fields per slot

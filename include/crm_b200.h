@@ -201,6 +201,15 @@ int crm_sim_set_exact_math(crm_sim* sim, int exact);
 int crm_sim_set_skin(crm_sim* sim, float skin);
 /* Steps that rebuilt the structure / steps that reused it. */
 int crm_sim_list_stats(const crm_sim* sim, uint64_t* n_builds, uint64_t* n_eval_steps);
+/* Divisions while the structure is live do not force a new search: the rows of the daughters and of the
+ * mothers' neighbours are rebuilt from candidate lists (the reference re-sorts its voxels every step;
+ * cellular_raza chili update_cell_cycle + sort_cells_in_subdomains).  Count of division steps absorbed
+ * that way, and the switch (default on; CRM_B200_PATCH=0). */
+uint64_t crm_sim_patch_count(const crm_sim* sim);
+/* Interaction forces the last step used ([n_rods][n_vertices][3]; rods created by that step's divisions
+ * read zero): lets a test compare a list step with a fresh search of the same positions. */
+int crm_sim_last_forces(crm_sim* sim, float* out_force);
+int crm_sim_set_patching(crm_sim* sim, int on);
 
 uint32_t crm_sim_n_rods(const crm_sim* sim);
 uint32_t crm_sim_n_vertices(const crm_sim* sim);

@@ -264,3 +264,61 @@ def test_step_begin_end_on_a_caller_stream(product_lib):
     assert a.list_stats() == b.list_stats()
     a.close()
     b.close()
+
+
+def test_divisions_patch_the_live_neighbour_structure(product_lib):
+    """Dense colony with divisions in most steps: the persistent structure is patched (rows of the daughters
+    and of the mothers' neighbours rebuilt from candidate lists) instead of searching again after every
+    division.  Same trajectories and lineage as with a search after every division and as the oracle."""
+    n = 700
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.05)
+    pos = lattice_colony(n, seed=21)
+    par = mie_params(n, growth_rate=0.1)
+    rng = np.random.default_rng(6)
+    par["growth_setter_kind"] = _capi.SETTER_EXPLICIT
+    par["growth_setter_a"] = 0.1
+    par["growth_setter_b"] = 0.1
+    par["spring_length_threshold"] = rng.uniform(3.0, 3.3, n).astype(np.float32)
+    par["threshold_setter_kind"] = _capi.SETTER_EXPLICIT
+    par["threshold_setter_a"] = 6.0
+    par["threshold_setter_b"] = 6.0
+    steps = 40
+    out = {}
+    for patching in (1, 0):
+        g = _capi.Sim(product_lib, cfg)
+        product_lib.check(product_lib.fn("sim_set_patching")(g.h, patching))
+        g.set_agents(pos, np.zeros_like(pos), par)
+        g.step(steps)
+        out[patching] = (g.get_state(), g.list_stats(), g.patch_count())
+        g.close()
+    o = oracle.sim(cfg)
+    o.set_agents(pos, np.zeros_like(pos), par)
+    o.step(steps)
+    po, vo, paro, ido, pro = o.get_state()
+    (p1, v1, par1, id1, pr1), st1, np1 = out[1]
+    (p0, v0, par0, id0, pr0), st0, np0 = out[0]
+    assert len(po) > 1.5 * n  # most rods divided
+    assert np0 == 0 and np1 >= 10, (np0, np1)
+    # the interaction forces of a list step right after patched divisions equal a fresh search of the same state
+    g = _capi.Sim(product_lib, cfg)
+    g.set_agents(pos, np.zeros_like(pos), par)
+    g.step(6)
+    assert g.patch_count() >= 4
+    pb, vb, qb = g.get_state()[:3]
+    g.step(1)
+    assert g.list_stats()["eval_steps"] >= 5
+    f_list = g.last_forces()[:len(pb)]
+    g.close()
+    c = _capi.Sim(product_lib, cfg)
+    c.set_agents(pb, vb, qb)
+    f_search, _ = c.compute_forces()
+    c.close()
+    assert _force_err(f_list, f_search) < FORCE_RTOL
+    assert st1["builds"] < st0["builds"] and st1["eval_steps"] > st0["eval_steps"] + 10, (st1, st0)
+    for p, idg, prg, parg in ((p1, id1, pr1, par1), (p0, id0, pr0, par0)):
+        assert p.shape == po.shape
+        assert (idg == ido).all() and (prg == pro).all()
+        assert np.abs(p - po).max() < TRAJ_ATOL, np.abs(p - po).max()
+        assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
+    assert np.abs(p1 - p0).max() < 5e-5
