@@ -154,3 +154,39 @@ def _with_ny(kw, ny):
     kw = dict(kw)
     kw["_ny"] = ny
     return kw
+
+
+def multilayer_colony(n_rods: int, layers: int = 3, spacing=(27.0, 6.5), layer_height: float = 5.6, z0: float = 1.5,
+                      tilt_std: float = 0.01, seed: int = 777, margin: float = 16.0, **kw):
+    """C4 start state: ``layers`` stacked nematic lattices, every second one shifted by
+    half a lattice cell, rods slightly tilted out of the plane.  Returns (pos, domain edge, height)."""
+    per = int(np.ceil(n_rods / layers))
+    L = lattice_domain(per, spacing=spacing, margin=margin)
+    rng = np.random.default_rng(seed)
+    out = []
+    for k in range(layers):
+        n = min(per, n_rods - k * per)
+        p = lattice_colony(n, spacing=spacing, margin=margin, seed=seed + 1 + k, z=z0 + k * layer_height, **kw)
+        if k % 2:
+            p[:, :, 0] += np.float32(0.5 * spacing[0] - 0.01)
+            p[:, :, 1] += np.float32(0.5 * spacing[1] - 0.01)
+        tilt = rng.normal(0.0, tilt_std, n).astype(np.float32)
+        t = p[:, :, 0] - p[:, :, 0].mean(axis=1, keepdims=True)
+        p[:, :, 2] += tilt[:, None] * t
+        out.append(p)
+    pos = np.concatenate(out).astype(np.float32)
+    return pos, float(L + 0.5 * spacing[0]), float(max(20.0, z0 + layers * layer_height + 4.0))
+
+
+def multilayer_params(n: int, diffusion_constant: float = 0.03, growth_rate: float = 0.005, **kw) -> np.ndarray:
+    """``produce_ml_config`` agent values (reference cr_mech_coli/crm_multilayer/runner.py:52-76): Morse
+    radius 3, stiffness 1, strength 0.03, damping 0.02, tension 10, rigidity 20, threshold 20,
+    neighbour reduction (200, 0.5)."""
+    p = morse_params(n, radius=3.0, potential_stiffness=1.0, cutoff=10.0, strength=0.03, damping=0.02,
+                     spring_tension=10.0, rigidity=20.0, diffusion_constant=diffusion_constant,
+                     growth_rate=growth_rate, neighbor_reduction=(200, 0.5))
+    p["spring_length_threshold"] = 20.0
+    p["threshold_setter_a"] = 20.0
+    p["threshold_setter_b"] = 20.0
+    _apply(p, kw)
+    return p

@@ -322,3 +322,35 @@ def test_divisions_patch_the_live_neighbour_structure(product_lib):
         assert np.abs(p - po).max() < TRAJ_ATOL, np.abs(p - po).max()
         assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
     assert np.abs(p1 - p0).max() < 5e-5
+
+
+def test_multilayer_3d_trajectory(product_lib):
+    """C4 in small: stacked layers in 3D with the produce_ml_config parameters (gel pressure pushes the
+    layers together and onto z = 0, surface friction, weak damping, neighbour-reduced growth, staggered
+    divisions); diffusion off so that the run is deterministic."""
+    from cr_mech_coli_b200.testing import multilayer_colony, multilayer_params
+
+    pos, L, H = multilayer_colony(180)
+    cfg = _capi.make_config(domain_size=(L, L), domain_height=H, n_voxels=(max(1, int(L // 40)),) * 2, dt=0.025,
+                            t_max=2.0, n_saves=3, gel_pressure=0.1, surface_friction=0.03,
+                            surface_friction_distance=0.3)
+    par = multilayer_params(len(pos), diffusion_constant=0.0, growth_rate=0.05)
+    par["growth_setter_kind"] = _capi.SETTER_EXPLICIT
+    par["growth_setter_b"] = 0.05
+    par["spring_length_threshold"] = np.random.default_rng(5).uniform(3.05, 3.6, len(par)).astype(np.float32)
+    g = _capi.Sim(product_lib, cfg)
+    o = oracle.sim(cfg, openmp=True)
+    g.set_agents(pos, np.zeros_like(pos), par)
+    o.set_agents(pos, np.zeros_like(pos), par)
+    g.run()
+    o.run()
+    sg, so = g.snapshots(), o.snapshots()
+    assert [s[0] for s in sg] == [s[0] for s in so] and len(sg) == 5
+    for (it, pg, vg, parg, idg, prg), (_, po, vo, paro, ido, pro) in zip(sg, so):
+        assert pg.shape == po.shape, f"rod count differs at iteration {it}"
+        assert (idg == ido).all() and (prg == pro).all(), f"lineage differs at iteration {it}"
+        assert (parg["spring_length"] == paro["spring_length"]).all()
+        assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
+        assert np.abs(pg - po).max() < TRAJ_ATOL, f"iteration {it}: {np.abs(pg - po).max()}"
+    assert len(sg[-1][1]) > len(pos)  # some rods divided
+    assert sg[-1][1][:, :, 2].max() < pos[:, :, 2].max() - 0.05  # the gel pressure moved the top layer down
