@@ -102,6 +102,20 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def pinned_copy(lib, a):
+    b = lib.pinned_empty(a.shape, a.dtype)
+    b[...] = a
+    return b
+
+
+def state_buffers(lib, n, nv):
+    """Page-locked (pos, vel, params, ids, parents) for Sim.get_state(out=...)."""
+    from cr_mech_coli_b200 import _capi
+    return (lib.pinned_empty((n, nv, 3), np.float32), lib.pinned_empty((n, nv, 3), np.float32),
+            lib.pinned_empty(n, _capi.ROD_PARAMS_DTYPE), lib.pinned_empty(n, _capi.IDENT_DTYPE),
+            lib.pinned_empty(n, _capi.IDENT_DTYPE))
+
+
 def measured_peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -217,11 +231,14 @@ def main():
         sim.close()
 
         # e2e: host buffers in, K steps, host buffers out, through the C ABI
+        # (inputs and outputs live in page-locked host memory, crm_host_alloc)
+        pos, vel, par = pinned_copy(lib, pos), pinned_copy(lib, vel), pinned_copy(lib, par)
+        out = state_buffers(lib, n, pos.shape[1])
         sim2 = _capi.Sim(lib, cfg, device)
         t0 = time.perf_counter()
         sim2.set_agents(pos, vel, par)
         sim2.step(K)
-        pos_out = sim2.get_state()[0]
+        pos_out = sim2.get_state(out=out)[0]
         e2e_s = time.perf_counter() - t0
         assert np.isfinite(pos_out).all()
         h2d = pos.nbytes + vel.nbytes + n * (32 + 16 + 16 + 48 + 4)
@@ -279,12 +296,14 @@ def main():
         ds.close()
 
         # e2e: host buffers in, K sharded steps, host buffers out
+        pos, vel, par = pinned_copy(lib, pos), pinned_copy(lib, vel), pinned_copy(lib, par)
+        out = state_buffers(lib, n, pos.shape[1])
         ds2 = sharded.DistributedShard(lib, cfg, part, device)
         barrier()
         t0 = time.perf_counter()
         ds2.set_agents_local(pos, vel, par, gsl, n_total=n * world)
         ds2.step(K)
-        pos_out = ds2.shard.sim.get_state()[0]
+        pos_out = ds2.shard.sim.get_state(out=out)[0]
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
         barrier()

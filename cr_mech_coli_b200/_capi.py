@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 from pathlib import Path
 
 import numpy as np
@@ -197,6 +198,8 @@ class Library:
             "sim_apply_divisions": (C.c_int, [vp, vp, vp, vp, u32]),
             "sim_take_snapshot": (C.c_int, [vp]),
             "sim_snapshot_global_slots": (C.c_int, [vp, u32, vp]),
+            "host_alloc": (vp, [C.c_size_t]),
+            "host_free": (None, [vp]),
             # oracle only
             "sim_pairs_in_cutoff": (u64, [vp]),
             "num_threads": (C.c_int, []),
@@ -217,6 +220,20 @@ class Library:
             kind = STATUS_NAMES.get(rc, f"error {rc}")
             raise SimulationError(f"{kind}: {self.last_error()}")
         return rc
+
+    def pinned_empty(self, shape, dtype) -> np.ndarray:
+        """Uninitialised array in page-locked host memory (``crm_host_alloc``): buffers for
+        ``Sim.set_agents`` / ``Sim.get_state(out=...)`` that cross the bus at link speed."""
+        dtype = np.dtype(dtype)
+        shape = (shape,) if np.isscalar(shape) else tuple(shape)
+        nbytes = int(np.prod(shape, dtype=np.int64)) * dtype.itemsize
+        ptr = self.fn("host_alloc")(nbytes)
+        if not ptr:
+            raise MemoryError(self.last_error())
+        buf = (C.c_char * max(nbytes, 1)).from_address(ptr)
+        arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes).view(dtype).reshape(shape)
+        weakref.finalize(buf, self.fn("host_free"), ptr)  # freed when the last view of the block dies
+        return arr
 
     def save_schedule(self, cfg: CrmConfig):
         out = np.zeros(int(cfg.n_saves) + 2, dtype=np.uint64)
@@ -341,13 +358,25 @@ class Sim:
         self.L.check(self.L.fn("sim_compute_forces")(self.h, _fptr(force), _fptr(nn)))
         return force, nn
 
-    def get_state(self):
+    def get_state(self, out=None):
+        """(pos, vel, params, ids, parents) in slot order.  ``out`` = the same five arrays to fill
+        (e.g. page-locked ones from ``Library.pinned_empty``), sized for at least ``n_rods``."""
         n, nv = self.n_rods, self.n_vertices
-        pos = np.zeros((n, nv, 3), dtype=np.float32)
-        vel = np.zeros((n, nv, 3), dtype=np.float32)
-        par = np.zeros(n, dtype=ROD_PARAMS_DTYPE)
-        ids = np.zeros(n, dtype=IDENT_DTYPE)
-        parents = np.zeros(n, dtype=IDENT_DTYPE)
+        if out is not None:
+            want = [((n, nv, 3), np.float32), ((n, nv, 3), np.float32), ((n,), ROD_PARAMS_DTYPE), ((n,), IDENT_DTYPE),
+                    ((n,), IDENT_DTYPE)]
+            got = []
+            for a, (shape, dt) in zip(out, want):
+                if a.dtype != dt or not a.flags.c_contiguous or a.shape[1:] != shape[1:] or a.shape[0] < n:
+                    raise ValueError("out arrays must be C-contiguous, typed like get_state()'s and hold n_rods rows")
+                got.append(a[:n])
+            pos, vel, par, ids, parents = got
+        else:
+            pos = np.empty((n, nv, 3), dtype=np.float32)
+            vel = np.empty((n, nv, 3), dtype=np.float32)
+            par = np.empty(n, dtype=ROD_PARAMS_DTYPE)
+            ids = np.empty(n, dtype=IDENT_DTYPE)
+            parents = np.empty(n, dtype=IDENT_DTYPE)
         self.L.check(
             self.L.fn("sim_get_state")(self.h, _fptr(pos), _fptr(vel), _fptr(par), _fptr(ids), _fptr(parents))
         )

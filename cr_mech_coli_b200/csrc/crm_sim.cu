@@ -19,14 +19,31 @@ int crm_fail(int code, const char* fmt, ...) {
 }
 #define fail crm_fail
 
+// Work split over host threads (upload / download of 1e6-rod parameter blocks is host-bound otherwise).
+template <class F>
+static void parallel_for(size_t n, F f) {
+    const unsigned hw = std::thread::hardware_concurrency();
+    const size_t nt = std::min<size_t>(std::min<unsigned>(hw ? hw : 1u, 16u), n / 16384);
+    if (nt <= 1) {
+        f((size_t)0, n);
+        return;
+    }
+    std::vector<std::thread> th;
+    const size_t chunk = (n + nt - 1) / nt;
+    for (size_t t = 1; t < nt; ++t) th.emplace_back([=] { f(std::min(n, t * chunk), std::min(n, (t + 1) * chunk)); });
+    f((size_t)0, std::min(n, chunk));
+    for (auto& t : th) t.join();
+}
+
+// new zeroed array holding the first `old_count` elements of the old one; the old block is freed by the
+// caller after ONE synchronisation for all arrays (`retired`)
 template <class T>
-static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st) {
+static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st, std::vector<void*>& retired) {
     T* np_ = nullptr;
     CK(cudaMalloc(&np_, sizeof(T) * new_count));
     CK(cudaMemsetAsync(np_, 0, sizeof(T) * new_count, st));
     if (ptr && old_count) CK(cudaMemcpyAsync(np_, ptr, sizeof(T) * old_count, cudaMemcpyDeviceToDevice, st));
-    CK(cudaStreamSynchronize(st));
-    if (ptr) CK(cudaFree(ptr));
+    if (ptr) retired.push_back(ptr);
     ptr = np_;
     return 0;
 }
@@ -40,7 +57,8 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     const size_t st_ = (size_t)3 * s->lp;
     const size_t on = s->n, oc = (size_t)s->n * st_;
     int rc;
-#define G(p, cnt_old, cnt_new) if ((rc = regrow(p, cnt_old, cnt_new, s->stream))) return rc
+    std::vector<void*> retired;
+#define G(p, cnt_old, cnt_new) if ((rc = regrow(p, cnt_old, cnt_new, s->stream, retired))) return rc
     G(s->d.pos, oc, cap * st_);
     G(s->d.vel, oc, cap * st_);
     G(s->d.force, oc, cap * st_);
@@ -83,7 +101,10 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.chord_sorted, 0, (size_t)2 * cap);
     G(s->d.divlist, 0, (size_t)cap);
     G(s->stage, 0, (size_t)cap * s->nv * 3);
+    G(s->stage2, 0, (size_t)cap * s->nv * 3);
 #undef G
+    CK(cudaStreamSynchronize(s->stream));
+    for (void* q : retired) CK(cudaFree(q));
     s->d.divcap = cap;
     s->d.tile = s->sim_of.empty() ? nullptr : s->tile_buf;
     s->cap = cap;
@@ -137,11 +158,23 @@ static float cutoff_threshold(float c) {
     return x;
 }
 
-void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams& mech, GrowState& grow,
-                               CycleParams& cyc) {
+// The constants that cost something (two powf, the cutoff search) repeat from rod to rod in every real
+// colony: remembered for the last distinct (cutoff), (en, em) seen.  Same bits as computing them afresh.
+struct ParamCache {
+    bool has_c = false, has_m = false;
+    float cutoff = 0, cutoff2 = 0, en = 0, em = 0, C = 0, d = 0;
+};
+
+static void fill_device_params_cached(const crm_rod_params& p, ParamCache& k, PotParams& pot, MechParams& mech,
+                                      GrowState& grow, CycleParams& cyc) {
     pot.type = p.potential;
     pot.radius = p.radius;
-    pot.cutoff2 = cutoff_threshold(p.cutoff);
+    if (!k.has_c || memcmp(&k.cutoff, &p.cutoff, sizeof(float)) != 0) {
+        k.cutoff = p.cutoff;
+        k.cutoff2 = cutoff_threshold(p.cutoff);
+        k.has_c = true;
+    }
+    pot.cutoff2 = k.cutoff2;
     if (p.potential == CRM_POT_MORSE) {
         pot.strength = p.strength;
         pot.a = p.potential_stiffness;
@@ -149,12 +182,18 @@ void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams&
     } else {
         // same f32 operation order as the reference's `strength * mie_constant * part`
         const float en = p.en, em = p.em;
-        const float C = en / (en - em) * powf(en / em, en / (en - em));
-        pot.strength = p.strength * C;
+        if (!k.has_m || memcmp(&k.en, &en, sizeof(float)) != 0 || memcmp(&k.em, &em, sizeof(float)) != 0) {
+            k.en = en;
+            k.em = em;
+            k.C = en / (en - em) * powf(en / em, en / (en - em));
+            k.d = powf(em / en, 1.0f / (en - em));
+            k.has_m = true;
+        }
+        pot.strength = p.strength * k.C;
         pot.a = p.bound;
         pot.b = en;
         pot.c = em;
-        pot.d = powf(em / en, 1.0f / (en - em));
+        pot.d = k.d;
     }
     mech = make_float4(p.spring_tension, p.rigidity, p.damping, p.diffusion_constant);
     grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, 0.0f);
@@ -168,6 +207,12 @@ void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams&
     cyc.has_nr = p.has_neighbor_reduction;
     cyc.nr_max = p.neighbor_reduction_max;
     cyc.nr_exp = p.neighbor_reduction_exp;
+}
+
+void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams& mech, GrowState& grow,
+                            CycleParams& cyc) {
+    ParamCache k;
+    fill_device_params_cached(p, k, pot, mech, grow, cyc);
 }
 
 int crm_read_status(crm_sim* s) {
@@ -486,29 +531,33 @@ static int step_once(crm_sim* s) {
 static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
     const size_t m = (size_t)s->n * s->nv * 3;
     if (s->n == 0) return 0;
+    // everything is enqueued first (two staging buffers), ONE wait; into pinned caller buffers the copies
+    // run at bus speed while nothing else blocks
     if (pos) {
         launch_pack(s->nv, s->d.pos, s->stage, s->n, s->stream);
         CK(cudaMemcpyAsync(pos, s->stage, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
-        CK(cudaStreamSynchronize(s->stream));
     }
     if (vel) {
-        launch_pack(s->nv, s->d.vel, s->stage, s->n, s->stream);
-        CK(cudaMemcpyAsync(vel, s->stage, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
-        CK(cudaStreamSynchronize(s->stream));
+        launch_pack(s->nv, s->d.vel, s->stage2, s->n, s->stream);
+        CK(cudaMemcpyAsync(vel, s->stage2, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
     }
+    crm_hvec<GrowState> g(par ? s->n : 0);
+    crm_hvec<uint32_t> nn(par ? s->n : 0);
     if (par) {
-        std::vector<GrowState> g(s->n);
-        std::vector<uint32_t> nn(s->n);
         CK(cudaMemcpyAsync(g.data(), s->d.grow, sizeof(GrowState) * s->n, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaMemcpyAsync(nn.data(), s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
-        CK(cudaStreamSynchronize(s->stream));
-        for (uint32_t a = 0; a < s->n; ++a) {
-            par[a] = s->base[a];
-            par[a].growth_rate = g[a].x;
-            par[a].spring_length_threshold = g[a].y;
-            par[a].spring_length = g[a].z;
-            par[a].n_neighbors = nn[a];
-        }
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    if (par) {
+        parallel_for(s->n, [&](size_t a0, size_t a1) {
+            for (size_t a = a0; a < a1; ++a) {
+                par[a] = s->base[a];
+                par[a].growth_rate = g[a].x;
+                par[a].spring_length_threshold = g[a].y;
+                par[a].spring_length = g[a].z;
+                par[a].n_neighbors = nn[a];
+            }
+        });
     }
     return 0;
 }
@@ -665,7 +714,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->iteration = 0;
     s->snaps.clear();
     std::fill(s->vox_counter.begin(), s->vox_counter.end(), 0);
-    s->base.assign(par, par + n);
+    s->base.resize(n);
     s->ids.resize(n);
     s->parents.resize(n);
     s->gslot.resize(n);
@@ -677,23 +726,54 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->d.tile = nullptr;
     s->d.sim_fail = nullptr;
     s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1], 0);
-    std::vector<PotParams> pot(n);
-    std::vector<MechParams> mech(n);
-    std::vector<GrowState> grow(n);
-    std::vector<CycleParams> cyc(n);
-    std::vector<uint32_t> nn(n);
-    float rmax = 0.0f, cmax = 0.0f;
-    for (uint32_t a = 0; a < n; ++a) {
-        s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, a};
-        s->gslot[a] = a;
-        s->parents[a] = crm_ident{-1, 0, 0};
-        if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE)
-            return fail(CRM_ERR_INVALID, "rod %u: unknown potential %d", a, par[a].potential);
-        crm_fill_device_params(par[a], pot[a], mech[a], grow[a], cyc[a]);
-        nn[a] = par[a].n_neighbors;
-        rmax = std::max(rmax, par[a].radius);
-        cmax = std::max(cmax, par[a].cutoff);
+    const size_t m = (size_t)n * nv * 3;
+    if (n) {
+        // positions and velocities go first: from pinned caller buffers these copies run while the host
+        // threads below convert the parameter records
+        CK(cudaMemcpyAsync(s->stage, pos, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
+        launch_unpack(s->nv, s->stage, s->d.pos, n, s->stream);
+        CK(cudaMemcpyAsync(s->stage2, vel, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
+        launch_unpack(s->nv, s->stage2, s->d.vel, n, s->stream);
     }
+    crm_hvec<PotParams> pot(n);
+    crm_hvec<MechParams> mech(n);
+    crm_hvec<GrowState> grow(n);
+    crm_hvec<CycleParams> cyc(n);
+    crm_hvec<uint32_t> nn(n);
+    std::atomic<uint32_t> bad{UINT32_MAX}, rbits{0}, cbits{0};
+    parallel_for(n, [&](size_t a0, size_t a1) {
+        ParamCache k;
+        float rmax = 0.0f, cmax = 0.0f;
+        for (size_t a = a0; a < a1; ++a) {
+            s->base[a] = par[a];
+            s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, (uint64_t)a};
+            s->gslot[a] = a;
+            s->parents[a] = crm_ident{-1, 0, 0};
+            if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE) {
+                uint32_t cur = bad.load();
+                while ((uint32_t)a < cur && !bad.compare_exchange_weak(cur, (uint32_t)a)) {}
+                continue;
+            }
+            fill_device_params_cached(par[a], k, pot[a], mech[a], grow[a], cyc[a]);
+            nn[a] = par[a].n_neighbors;
+            rmax = std::max(rmax, par[a].radius);
+            cmax = std::max(cmax, par[a].cutoff);
+        }
+        // non-negative floats order like their bit patterns
+        auto amax = [](std::atomic<uint32_t>& t, float v) {
+            if (!(v > 0.0f)) return;
+            const uint32_t b = __builtin_bit_cast(uint32_t, v);
+            uint32_t cur = t.load();
+            while (b > cur && !t.compare_exchange_weak(cur, b)) {}
+        };
+        amax(rbits, rmax);
+        amax(cbits, cmax);
+    });
+    if (bad.load() != UINT32_MAX) {
+        CK(cudaStreamSynchronize(s->stream));
+        return fail(CRM_ERR_INVALID, "rod %u: unknown potential %d", bad.load(), par[bad.load()].potential);
+    }
+    const float rmax = __builtin_bit_cast(float, rbits.load()), cmax = __builtin_bit_cast(float, cbits.load());
     s->rsearch = std::max(cmax, 2.0f * rmax * 0.70710678f) * 1.0001f;
     s->d.rsearch = search_radius(s);  // the bounds kernels bake it into the cull thresholds
     s->d.skin = s->skin;
@@ -703,13 +783,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->backoff = 8;
     s->evals_since_build = 0;
     s->steps_since_build = 0;
-    const size_t m = (size_t)n * nv * 3;
     if (n) {
-        CK(cudaMemcpyAsync(s->stage, pos, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
-        launch_unpack(s->nv, s->stage, s->d.pos, n, s->stream);
-        CK(cudaStreamSynchronize(s->stream));
-        CK(cudaMemcpyAsync(s->stage, vel, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
-        launch_unpack(s->nv, s->stage, s->d.vel, n, s->stream);
         CK(cudaMemcpyAsync(s->d.pot, pot.data(), sizeof(PotParams) * n, cudaMemcpyHostToDevice, s->stream));
         CK(cudaMemcpyAsync(s->d.mech, mech.data(), sizeof(MechParams) * n, cudaMemcpyHostToDevice, s->stream));
         CK(cudaMemcpyAsync(s->d.grow, grow.data(), sizeof(GrowState) * n, cudaMemcpyHostToDevice, s->stream));
@@ -1025,6 +1099,19 @@ uint32_t crm_sim_n_vertices(const crm_sim* s) { return (uint32_t)s->nv; }
 uint64_t crm_sim_iteration(const crm_sim* s) { return s->iteration; }
 uint64_t crm_sim_launch_count(const crm_sim* s) { return s->launches; }
 uint64_t crm_sim_rod_steps(const crm_sim* s) { return s->rod_steps; }
+
+void* crm_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        fail(CRM_ERR_CUDA, "cudaHostAlloc of %zu bytes failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+void crm_host_free(void* ptr) {
+    if (ptr) cudaFreeHost(ptr);
+}
 
 int crm_sim_get_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par, crm_ident* ids, crm_ident* parents) {
     CK(cudaSetDevice(s->device));

@@ -7,10 +7,25 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <string>
+#include <thread>
+#include <memory>
+#include <utility>
 #include <vector>
 
 #include "crm_device.cuh"
+
+// std::vector whose resize() leaves trivially constructible elements uninitialised: the 1e6-rod host
+// mirrors are written right after they are sized, a zero fill first would only cost bus time.
+template <class T>
+struct crm_default_init_alloc : std::allocator<T> {
+    template <class U> struct rebind { using other = crm_default_init_alloc<U>; };
+    using std::allocator<T>::allocator;
+    template <class U> void construct(U* p) noexcept(std::is_nothrow_default_constructible<U>::value) { ::new (static_cast<void*>(p)) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+};
+template <class T> using crm_hvec = std::vector<T, crm_default_init_alloc<T>>;
 
 namespace crm {
 // launchers (crm_mech.cu / crm_force.cu)
@@ -61,6 +76,7 @@ struct crm_sim {
     uint32_t ncells_cap = 0;
     crm::Dev d{};
     float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
+    float* stage2 = nullptr; // second one: positions and velocities cross the bus back to back
     crm::Status* h_status = nullptr;  // pinned
     float emax = 0.0f;        // max centroid->vertex extent over owned rods
     float emax_ghost = 0.0f;  // ... over the current ghost rods
@@ -87,7 +103,7 @@ struct crm_sim {
     uint32_t backoff = 8;       // next holdoff (doubles while the lists keep being useless)
     uint64_t n_builds = 0, n_eval_steps = 0;
     // host-side bookkeeping
-    std::vector<crm_rod_params> base;  // cold fields per slot
+    crm_hvec<crm_rod_params> base;  // cold fields per slot
     std::vector<crm_ident> ids, parents;
     std::vector<uint64_t> gslot;       // global slot (= slot of the unsharded run) per owned slot
     std::vector<uint64_t> vox_counter;   // [sim][user voxel]

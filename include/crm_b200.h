@@ -215,6 +215,14 @@ uint32_t crm_sim_n_rods(const crm_sim* sim);
 uint32_t crm_sim_n_vertices(const crm_sim* sim);
 uint64_t crm_sim_iteration(const crm_sim* sim);
 
+/* Page-locked host memory for the buffers handed to crm_sim_set_agents / crm_sim_get_state: from such
+ * buffers positions and velocities cross the bus at link speed and overlap the host-side parameter
+ * conversion (pageable buffers work too, through the driver's bounce buffers).  The reference copies its
+ * inputs out of numpy arrays (src/agent.rs:485-489) and hands back fresh copies (:522-525); this pair is
+ * what a binding uses to allocate those arrays.  crm_host_alloc returns NULL on failure. */
+void* crm_host_alloc(size_t bytes);
+void crm_host_free(void* ptr);
+
 /* Current state in slot order (any pointer may be NULL). */
 int crm_sim_get_state(crm_sim* sim, float* pos, float* vel, crm_rod_params* params,
                       crm_ident* ids, crm_ident* parents);

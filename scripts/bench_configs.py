@@ -17,7 +17,7 @@ from cr_mech_coli_b200.testing import morse_params, multilayer_colony, multilaye
 ap = argparse.ArgumentParser()
 ap.add_argument("--config", default="c2,c4")
 ap.add_argument("--c2-target", type=int, default=10_000)
-ap.add_argument("--c2-growth", default="0.1,0.03,0.01,0.003,0.001")
+ap.add_argument("--c2-growth", default="defaults:0.01,relaxed:0.03,relaxed:0.015,relaxed:0.007,relaxed:0.003")
 ap.add_argument("--c4-rods", type=int, default=200_000)
 ap.add_argument("--c4-steps", type=int, default=300)
 ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -43,14 +43,21 @@ def cpu_rate(cfg, pos, par, seconds):
             "sample": f"{o.n_rods} rods x {done} steps ({dt:.1f} s)"}
 
 
-def c2_attempt(growth):
-    L = 2000.0
-    cfg = _capi.make_config(domain_size=(L, L), domain_height=2.5, n_voxels=(40, 40), dt=0.1, t_max=1e6, n_saves=0)
+MECH = {"defaults": dict(dt=0.1, z=1.25, kw={}),
+        # produce_ml_config's mechanics in an exactly planar colony (z = 0: no out-of-plane rounding noise to amplify)
+        "relaxed": dict(dt=0.05, z=0.0, kw=dict(damping=0.02, spring_tension=10.0, rigidity=20.0, potential_stiffness=1.0,
+                                                 strength=0.03))}
+
+
+def c2_attempt(mech, growth):
+    L = 3000.0
+    m = MECH[mech]
+    cfg = _capi.make_config(domain_size=(L, L), domain_height=2.5, n_voxels=(60, 60), dt=m["dt"], t_max=1e6, n_saves=0)
     n0 = 16
     pos = random_colony(n0, 300.0, seed=3, z_spread=0.0)
     pos[:, :, :2] += np.float32(0.5 * (L - 300.0))
-    pos[:, :, 2] = 1.25
-    par = morse_params(n0, growth_rate=growth)
+    pos[:, :, 2] = m["z"]
+    par = morse_params(n0, growth_rate=growth, **m["kw"])
     par["growth_setter_kind"] = _capi.SETTER_EXPLICIT  # daughters get (1.1 g, 0.8 g): divisions desynchronise
     par["growth_setter_a"] = 1.1 * growth
     par["growth_setter_b"] = 0.8 * growth
@@ -73,11 +80,14 @@ def c2_attempt(growth):
         n_b = sim.n_rods
     except _capi.SimulationError as e:
         sim.close()
-        return {"growth_rate": growth, "rods_reached": curve[-1]["rods"] if curve else n0, "steps": steps,
+        return {"mechanics": mech, "growth_rate": growth, "rods_reached": curve[-1]["rods"] if curve else n0, "steps": steps,
                 "error": str(e)[:60] + " ... " + str(e)[-40:]}, None
     tm = sim.read_timers()
     p, v, q = sim.get_state()[:3]
-    out = {"growth_rate": growth, "steps_to_target": steps, "wall_seconds_to_target": grow_wall, "rods_timed": [n_a, n_b],
+    seg = np.linalg.norm(np.diff(p, axis=1), axis=2)
+    out = {"mechanics": mech, "mechanics_values": m["kw"] or "AgentSettings() defaults", "dt": m["dt"], "growth_rate": growth,
+           "segment_length_range": [float(seg.min()), float(seg.max())], "colony_extent_um": float(np.ptp(p[:, :, 0])),
+           "steps_to_target": steps, "wall_seconds_to_target": grow_wall, "rods_timed": [n_a, n_b],
            "ms_per_step": ms / 200, "agent_steps_per_s": 0.5 * (n_a + n_b) * 200 / (ms * 1e-3),
            "force_ms": tm["force_ms"] / max(tm["force_launches"], 1), "neighbour_lists": sim.list_stats(),
            "patched_divisions": sim.patch_count(), "z_range": [float(p[:, :, 2].min()), float(p[:, :, 2].max())],
@@ -87,13 +97,16 @@ def c2_attempt(growth):
 
 
 def c2():
-    """The reference's model buckles out of its 2.5-um-high domain when the colony grows faster than it
-    relaxes (BoundaryError, in the oracle at the same iteration): growth rates are tried in descending
-    order and the first one that reaches the target is the timed one; the failures are reported."""
-    out = {"workload": f"C2: 2D colony grown from 16 rods (Morse defaults, Explicit 6/6 thresholds, dt 0.1, domain "
-                       f"2000^2 x 2.5) until >= {args.c2_target} rods, then 200 timed steps", "attempts": []}
-    for growth in [float(x) for x in args.c2_growth.split(",")]:
-        res, state = c2_attempt(growth)
+    """With AgentSettings() defaults the reference's model cannot carry a colony of this size: growth
+    compresses the interior faster than damping 1 lets it relax, rods buckle out of the 2.5-um-high domain
+    (BoundaryError) or, kept in plane, collapse (CalcError) - in the oracle at the same iteration, for every
+    growth rate from 0.1 down to 0.001 (profiles/configs_r01_c2_buckling.jsonl).  (mechanics, growth rate)
+    pairs are tried in order; the first that reaches the target is the timed one, failures are reported."""
+    out = {"workload": f"C2: 2D colony grown from 16 rods (Morse, Explicit 6/6 thresholds, domain 3000^2 x 2.5) until "
+                       f">= {args.c2_target} rods, then 200 timed steps", "attempts": []}
+    for spec in args.c2_growth.split(","):
+        mech, growth = spec.split(":")
+        res, state = c2_attempt(mech, float(growth))
         if state is None:
             out["attempts"].append(res)
             continue
@@ -116,6 +129,8 @@ def c4():
     sim = _capi.Sim(lib, cfg, 0)
     sim.set_agents(pos, np.zeros_like(pos), par)
     sim.step(20)
+    sim.compute_forces()  # instrumented launch: ordered pairs within the cutoff
+    pairs = sim.read_timers()
     sim.enable_timers(True)
     n_a = sim.n_rods
     ms = sim.step_timed(args.c4_steps)
@@ -129,6 +144,9 @@ def c4():
            "steps": args.c4_steps, "rods_timed": [n_a, n_b], "ms_per_step": ms / args.c4_steps,
            "agent_steps_per_s": 0.5 * (n_a + n_b) * args.c4_steps / (ms * 1e-3),
            "force_ms": tm["force_ms"] / max(tm["force_launches"], 1), "neighbour_lists": sim.list_stats(),
+           "ordered_pairs_in_cutoff": pairs["pairs_in_cutoff"], "neighbours_per_rod": pairs["pairs_in_cutoff"] / n_a,
+           "force_kernel_algorithmic_tflops": pairs["pairs_in_cutoff"] * 56 * 59.0 /
+                                              (tm["force_ms"] / max(tm["force_launches"], 1) * 1e-3) * 1e-12,
            "patched_divisions": sim.patch_count(), "z_range_after": [float(p[:, :, 2].min()), float(p[:, :, 2].max())]}
     sim.close()
     if not args.no_cpu:

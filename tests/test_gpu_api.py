@@ -61,3 +61,40 @@ def test_simulation_error_is_raised(product_lib):
 def test_empty_agent_list(product_lib):
     cc = crm.run_simulation_with_agents(crm.Configuration(t_max=1.0, n_saves=1), [])
     assert cc.get_all_iterations() == [0, 5, 10] and cc.get_cells_at_iteration(5) == {}
+
+
+def test_pinned_buffers_round_trip(product_lib):
+    """crm_host_alloc buffers in, get_state(out=...) buffers out: same values as the pageable path."""
+    import numpy as np
+    from cr_mech_coli_b200 import _capi
+    from cr_mech_coli_b200.testing import lattice_colony, lattice_domain, mie_params
+
+    n = 40_000  # above the host-thread split of the parameter conversion
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), dt=0.01, t_max=1e6, n_saves=0)
+    pos = lattice_colony(n, seed=3)
+    par = mie_params(n, growth_rate=0.0)
+    par["en"][::7] = 5.0  # the constant cache must follow every change of (en, em, cutoff)
+    par["cutoff"][::5] = 5.5
+    a = _capi.Sim(product_lib, cfg)
+    a.set_agents(pos, np.zeros_like(pos), par)
+    a.step(3)
+    ref = a.get_state()
+    fa = a.last_forces()
+    pp = [product_lib.pinned_empty(x.shape, x.dtype) for x in (pos, pos, par)]
+    pp[0][...] = pos
+    pp[1][...] = 0
+    pp[2][...] = par
+    out = (product_lib.pinned_empty((n + 5, 8, 3), np.float32), product_lib.pinned_empty((n, 8, 3), np.float32),
+           product_lib.pinned_empty(n, _capi.ROD_PARAMS_DTYPE), product_lib.pinned_empty(n, _capi.IDENT_DTYPE),
+           product_lib.pinned_empty(n, _capi.IDENT_DTYPE))
+    b = _capi.Sim(product_lib, cfg)
+    b.set_agents(*pp)
+    b.step(3)
+    got = b.get_state(out=out)
+    assert got[0].base is not None and len(got[0]) == n
+    for x, y in zip(ref, got):
+        assert x.tobytes() == y.tobytes()
+    assert fa.tobytes() == b.last_forces().tobytes()
+    with pytest.raises(ValueError):
+        b.get_state(out=(out[0][: n - 1],) + out[1:])
