@@ -111,7 +111,7 @@ def test_population_costs_equal_standalone_oracle_runs(product_lib):
     o = s.generate_optimization_infos(n)
     lo, hi = np.array(o.bounds_lower), np.array(o.bounds_upper)
     X = (lo + rng.uniform(0.2, 0.8, (6, len(lo))) * (hi - lo)).astype(np.float32)
-    X[3, 0] = np.nan  # a member whose run fails: costs error_cost, the others are untouched
+    X[3, 1] = np.nan  # damping: this member's run fails (CalcError) and costs error_cost, the others are untouched
     iterations = [0, 2, 4]
     got = crm_fit.predict_calculate_cost_population(X, data, iterations, s)
     assert got[3] == np.float32(s.constants.error_cost)
