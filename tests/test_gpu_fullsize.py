@@ -32,7 +32,8 @@ def test_momentum_balance(colony):
     scale = np.abs(force).astype(np.float64).sum(axis=(0, 1))
     assert scale[0] > 0 and scale[1] > 0
     assert np.all(np.abs(total[:2]) < 1e-6 * scale[:2]), (total, scale)
-    assert total[2] == 0.0 and scale[2] == 0.0  # exactly planar colony: no z force at all
+    # planar colony: z forces are rounding residue of `a(1-t) + bt` at z = 1.25 (reproduced from the reference)
+    assert np.abs(force[:, :, 2]).max() < 1e-5 * np.abs(force).max()
 
 
 @pytest.mark.parametrize("corner", [(0.0, 0.0), (0.47, 0.52), (0.93, 0.9)])
@@ -85,5 +86,7 @@ def test_list_steps_equal_search_steps(colony, product_lib):
         sim.close()
     assert out[0][1]["eval_steps"] >= 15 and out[1][1]["eval_steps"] == 0
     assert np.isfinite(out[0][0]).all()
-    assert np.abs(out[0][0] - out[1][0]).max() < 2e-5
+    # coordinates reach 1e4 um (one ulp = 1e-3 um): compare in units in the last place
+    ulps = np.abs(out[0][0] - out[1][0]) / np.spacing(np.abs(out[1][0]))
+    assert ulps.max() <= 4.0, ulps.max()
     assert np.abs(out[0][0] - pos).max() > 1e-4  # the colony did move

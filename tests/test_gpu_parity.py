@@ -354,3 +354,30 @@ def test_multilayer_3d_trajectory(product_lib):
         assert np.abs(pg - po).max() < TRAJ_ATOL, f"iteration {it}: {np.abs(pg - po).max()}"
     assert len(sg[-1][1]) > len(pos)  # some rods divided
     assert sg[-1][1][:, :, 2].max() < pos[:, :, 2].max() - 0.05  # the gel pressure moved the top layer down
+
+
+def test_list_steps_with_mixed_potentials(product_lib):
+    """Pairs of rods with different potentials take the per-entry path of the list kernel (the uniform
+    variant is only launched when the build queued no such pair): Morse and Mie rods of several radii."""
+    n = 900
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.05)
+    pos = lattice_colony(n, seed=21)
+    par = mie_params(n, growth_rate=0.0)
+    mo = morse_params(n, radius=1.4, cutoff=6.0, strength=0.05, growth_rate=0.0)
+    par[::3] = mo[::3]
+    par["radius"][1::4] = 1.3
+    par["spring_length_threshold"] = 1e30
+    outs = []
+    for uniform_colony in (False, True):
+        q = mie_params(n, growth_rate=0.0) if uniform_colony else par
+        q["spring_length_threshold"] = 1e30
+        g, o = _pair(cfg, pos, q, product_lib)
+        g.step(40)
+        o.step(40)
+        assert g.list_stats()["eval_steps"] >= 30
+        pg, po = g.get_state()[0], o.get_state()[0]
+        assert np.abs(pg - po).max() < TRAJ_ATOL
+        assert (g.get_state()[2]["n_neighbors"] == o.get_state()[2]["n_neighbors"]).all()
+        outs.append(pg)
+    assert np.abs(outs[0] - outs[1]).max() > 1e-3  # the two colonies do behave differently
