@@ -215,10 +215,17 @@ void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams&
     fill_device_params_cached(p, k, pot, mech, grow, cyc);
 }
 
+// what the (re)builds of the persistent structure reported about its rods; sticky until the next full build
+static void crm_note_list_flags(crm_sim* s) {
+    if (s->h_status->any_slow) s->lists_slow = true;
+    if (s->h_status->seen_morse) s->lists_morse = true;
+    if (s->h_status->seen_mie) s->lists_mie = true;
+}
+
 int crm_read_status(crm_sim* s) {
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
-    if (s->h_status->any_slow) s->lists_slow = true;
+    crm_note_list_flags(s);
     return 0;
 }
 
@@ -377,7 +384,7 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     s->launches += launch_binning(s->d, s->n_sims, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
-    if (build) s->lists_slow = false;  // until this step's status says otherwise (read before any list step)
+    if (build) s->lists_slow = s->lists_morse = s->lists_mie = false;  // until this step's status says otherwise (read before any list step)
     launch_force(s->nv, s->d, s->fast_math, count, build, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
     s->launches += 1;
@@ -400,7 +407,8 @@ static int launch_force_from_lists(crm_sim* s) {
         s->n_dirty = 0;
     }
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
-    launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow, s->stream);
+    launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow,
+                      s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE), s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
     s->launches += 1;
     return 0;
@@ -489,7 +497,7 @@ static int step_finish(crm_sim* s) {
     if (s->n == 0) return 0;
     int rc;
     CK(cudaStreamSynchronize(s->stream));
-    if (s->h_status->any_slow) s->lists_slow = true;
+    crm_note_list_flags(s);
     if (s->timers) {
         float ms = 0.0f;
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));

@@ -36,7 +36,7 @@ void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t 
 void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
 int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st);
 void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
-void launch_force_eval(int nv, const Dev& d, bool fast, bool uniform, cudaStream_t st);
+void launch_force_eval(int nv, const Dev& d, bool fast, bool uniform, int pot_type, cudaStream_t st);
 void launch_force_lists(int nv, const Dev& d, bool fast, cudaStream_t st);
 int launch_patch(const Dev& d, uint32_t n_div, uint32_t n0, int lp, int maxp, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
@@ -87,6 +87,7 @@ struct crm_sim {
     float skin = 0.5f;          // um; 0 disables the structure (every step searches from scratch)
     bool need_rebuild = true;   // the next step must search (and rebuild the structure)
     bool have_lists = false;    // the structure on the device describes the current slots
+    bool lists_morse = true, lists_mie = true;  // potential types among the rods of the structure (same protocol)
     bool lists_slow = true;     // ... and queues pairs with mixed potentials (known after the build step's status)
     bool want_rebuild = true;   // outcome of the last step: a local reason to rebuild (sharded runs: the
                                 // coordinator combines the slabs' wishes, crm_sim_keep_lists)
