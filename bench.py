@@ -369,5 +369,14 @@ def main():
     print(json.dumps(line))
 
 
+def _only_json_on_stdout():
+    """Libraries write to fd 1 (NCCL prints its version there): everything but the JSON line goes to stderr."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 if __name__ == "__main__":
+    _only_json_on_stdout()
     main()
