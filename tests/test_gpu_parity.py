@@ -381,3 +381,30 @@ def test_list_steps_with_mixed_potentials(product_lib):
         assert (g.get_state()[2]["n_neighbors"] == o.get_state()[2]["n_neighbors"]).all()
         outs.append(pg)
     assert np.abs(outs[0] - outs[1]).max() > 1e-3  # the two colonies do behave differently
+
+
+@pytest.mark.parametrize("nv,pot", [(3, "mie"), (5, "morse"), (12, "mie"), (16, "morse")])
+def test_list_steps_other_vertex_counts(product_lib, nv, pot):
+    """List steps (potential-type variants of the list kernel) for rods of 3 ... 16 vertices: more than 8
+    vertices use 16 lanes per rod and another queue-entry layout."""
+    n = 600 if nv <= 5 else 200  # the oracle evaluates nv (nv - 1) combinations for every pair of the voxel stencil
+    sl = 21.0 / (nv - 1)
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.02)
+    pos = lattice_colony(n, n_vertices=nv, spring_length=sl, seed=nv)
+    if pot == "mie":
+        par = mie_params(n, growth_rate=0.0, spring_length=sl)
+    else:
+        par = morse_params(n, radius=1.5, cutoff=6.0, strength=0.1, growth_rate=0.0, spring_length=sl)
+    par["spring_length_threshold"] = 1e30
+    g = _capi.Sim(product_lib, cfg)
+    o = oracle.sim(cfg, openmp=True)
+    g.set_agents(pos, np.zeros_like(pos), par)
+    o.set_agents(pos, np.zeros_like(pos), par)
+    g.step(30)
+    o.step(30)
+    assert g.list_stats()["eval_steps"] >= 20
+    sg, so = g.get_state(), o.get_state()
+    assert np.abs(sg[0] - so[0]).max() < TRAJ_ATOL
+    assert (sg[2]["n_neighbors"] == so[2]["n_neighbors"]).all()
+    assert np.abs(sg[0] - pos).max() > 1e-3
