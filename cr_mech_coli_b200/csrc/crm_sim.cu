@@ -488,6 +488,7 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaEventRecord(s->ev_status, s->stream));
     return 0;
 }
 
@@ -496,7 +497,9 @@ static int step_finish(crm_sim* s) {
     s->step_open = false;
     if (s->n == 0) return 0;
     int rc;
-    CK(cudaStreamSynchronize(s->stream));
+    // the step's own work only: what a caller enqueued behind it on the stream (the sharded coordinator's
+    // next halo exchange) keeps running while the host decides what the next step is
+    CK(cudaEventSynchronize(s->ev_status));
     crm_note_list_flags(s);
     if (s->timers) {
         float ms = 0.0f;
@@ -648,6 +651,7 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaMallocHost(&s->h_status, sizeof(Status) + 128));  // + pinned scratch (message headers)
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
+    CK(cudaEventCreateWithFlags(&s->ev_status, cudaEventDisableTiming));
     s->d.lx = c->domain_size[0];
     s->d.ly = c->domain_size[1];
     s->d.lz = c->domain_height;
@@ -677,6 +681,7 @@ void crm_sim_destroy(crm_sim* s) {
     if (s->h_status) cudaFreeHost(s->h_status);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev_status) cudaEventDestroy(s->ev_status);
     if (s->ev_t0) cudaEventDestroy(s->ev_t0);
     if (s->ev_t1) cudaEventDestroy(s->ev_t1);
     if (s->stream) cudaStreamSynchronize(s->stream);

@@ -135,6 +135,7 @@ struct crm_sim {
     // timers
     bool timers = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_status = nullptr;  // recorded behind the status read-back of a step: what step_finish waits for
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // crm_sim_timer_start / stop
     double force_ms = 0.0;
     uint64_t force_launches = 0;

@@ -613,6 +613,7 @@ class DistributedShard:
         if self._flags_all is None:
             self._flags_all = t.zeros(2 * self.world, dtype=t.int32, device=s.device)
             self._flags_host = t.zeros(2 * self.world, dtype=t.int32).pin_memory()
+            self._flags_event = t.cuda.Event()
         with t.cuda.stream(s.stream):
             if not self._halo_ahead:
                 self._frozen_halo()
@@ -620,14 +621,21 @@ class DistributedShard:
             s.step_begin()
             self.tr.dist.all_gather_into_tensor(self._flags_all, s.flags, group=self.tr.group)
             self._flags_host.copy_(self._flags_all, non_blocking=True)
+            self._flags_event.record(s.stream)
             # the halo of the NEXT step, enqueued while this one runs: it is what the next step needs if
             # no slab asks for a rebuild (the common case), and harmless otherwise (it only touches the
             # exchange buffers and ghost slots, which a rebuild step fills again)
             self._frozen_halo()
             self._halo_ahead = True
-        s.step_end()  # waits for the stream: the flags of all slabs are on the host as well
+        # the host waits for the flags only: the exchange above is still running when the next step's
+        # kernels are enqueued behind it, so the device never waits for the host
+        self._flags_event.synchronize()
+        s.step_end()
         self.moved = False
-        return self._flags_host.numpy().reshape(self.world, 2).astype(np.float64)
+        st = self._flags_host.numpy().reshape(self.world, 2).astype(np.float64)
+        if st[:, 1].max() > 0 or st[:, 0].sum() > 0:
+            s.stream.synchronize()  # the synchronous rebuild / division protocol follows: drain the stream first
+        return st
 
     def _frozen_halo(self):
         s = self.shard

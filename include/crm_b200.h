@@ -301,7 +301,9 @@ int crm_sim_set_ghosts_msgs(crm_sim* sim, const void* dev_msg_lo, const void* de
  *   crm_sim_ghosts_refresh  received records scattered to the ghost slots of the last rebuild step
  *   crm_sim_step_begin      the step enqueued; dev_flags[0..1] = {divisions, reason to rebuild}
  *                           written on the stream (device memory, may be NULL)
- *   crm_sim_step_end        one stream synchronisation + the host part of the step
+ *   crm_sim_step_end        one wait + the host part of the step.  It waits for the step's own work (an event
+ *                           behind its status read-back), not for what the caller enqueued on the stream after
+ *                           crm_sim_step_begin: the next halo exchange keeps running while the host decides
  * crm_sim_step(sim, 1) == crm_sim_step_begin(sim, NULL) + crm_sim_step_end(sim). */
 void* crm_sim_stream(const crm_sim* sim);
 /* ... or make the sim run on a stream the caller owns (it must outlive the sim). */
