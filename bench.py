@@ -59,16 +59,21 @@ class ClockSampler:
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index, enabled: bool = True):
+        """``gpu_index``: one index or a list (ONE nvidia-smi process polls them all: under torchrun rank 0
+        samples every GPU of the job, the other ranks none - eight pollers perturb a lock-step job)."""
         self.rows = []
         self.proc = None
-        self.idx = gpu_index
+        self.idx = ",".join(str(i) for i in gpu_index) if isinstance(gpu_index, (list, tuple)) else str(gpu_index)
+        self.enabled = enabled
 
     def start(self):
+        if not self.enabled:
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
-                 str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 self.idx], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -79,6 +84,8 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        if not self.enabled:
+            return None
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -280,7 +287,7 @@ def main():
         ds.step(W)
         ds.shard.sim.enable_timers(True)
         launches0 = ds.shard.sim.launch_count()
-        sampler = ClockSampler(device)
+        sampler = ClockSampler(list(range(min(world, ndev))), enabled=rank == 0)
         sampler.start()
         barrier()
         lib.check(lib.fn("sim_timer_start")(ds.shard.sim.h))

@@ -644,6 +644,18 @@ class DistributedShard:
         s.frozen_ghosts()
 
     def step(self, n_steps: int = 1):
+        """``n_steps`` collective steps.  The cyclic garbage collector is paused meanwhile: the ranks run in
+        lock step, so a collection on any of them is a stall of all of them."""
+        import gc
+        was_on = gc.isenabled()
+        gc.disable()
+        try:
+            self._steps(n_steps)
+        finally:
+            if was_on:
+                gc.enable()
+
+    def _steps(self, n_steps: int):
         for _ in range(n_steps):
             if STREAM_ORDERED and self.use_lists and not self.rebuild_next:
                 st = self._frozen_step()
