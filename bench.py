@@ -53,60 +53,93 @@ def workload(n_rods: int, seed: int = 12345):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons of this rank's GPU during the timed region (B200_PROFILING.md's clocks
+    line), polled in-process through NVML every 5 ms; falls back to one `nvidia-smi -lms` child when the NVML
+    binding is missing.  (A child per rank is slow to start next to a 20-ms timed region, and killing it in the
+    middle of its NVML initialisation stalled the following cudaMalloc calls of the job.)"""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
-    def __init__(self, gpu_index, enabled: bool = True):
-        """``gpu_index``: one index or a list (ONE nvidia-smi process polls them all: under torchrun rank 0
-        samples every GPU of the job, the other ranks none - eight pollers perturb a lock-step job)."""
-        self.rows = []
+    def __init__(self, gpu_index: int):
+        self.rows = []  # (sm MHz, max MHz, set of reasons)
         self.proc = None
-        self.idx = ",".join(str(i) for i in gpu_index) if isinstance(gpu_index, (list, tuple)) else str(gpu_index)
-        self.enabled = enabled
+        self.nvml = None
+        self.idx = int(gpu_index)
+        cvd = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        try:  # NVML and nvidia-smi count physical devices
+            self.idx = int(cvd.split(",")[self.idx]) if cvd else self.idx
+        except (ValueError, IndexError):
+            pass
+        self.halt = threading.Event()
+        self.t = None
 
     def start(self):
-        if not self.enabled:
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
             return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
-                 self.idx], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
-    def stop(self):
-        if not self.enabled:
-            return None
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+    def _poll(self):
+        nv = self.nvml
+        reasons_fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self.halt.is_set():
             try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-                for nm, v in zip(names, r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
+                mask = int(reasons_fn(self.handle))
+                self.rows.append((float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)), self.max_mhz,
+                                  {n for n, b in self.BITS.items() if mask & b}))
             except Exception:
                 pass
+            self.halt.wait(0.005)
+
+    def _read(self):
+        for line in self.proc.stdout:
+            r = [x.strip() for x in line.split(",")]
+            try:
+                self.rows.append((float(r[1]), float(r[2]),
+                                  {n for n, v in zip(self.NAMES, r[5:9]) if v.lower().startswith("active")}))
+            except Exception:
+                pass
+
+    def stop(self):
+        if self.nvml is None and not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML binding and no nvidia-smi"]}
+        if self.nvml is not None:
+            self.halt.set()
+            self.t.join(timeout=1.0)
+            source = "nvml, 5 ms"
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+            source = "nvidia-smi -lms 100"
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = set().union(*[r[2] for r in self.rows]) if self.rows else set()
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": source}
 
 
 def pinned_copy(lib, a):
@@ -148,8 +181,8 @@ def cpu_baseline(n_sample: int, steps: int, threads: int | None):
 
     cfg, pos, par = workload(n_sample)
     lib = oracle.library(openmp=True)
-    if threads:
-        lib.fn("set_num_threads")(threads)
+    # all host cores unless told otherwise (torchrun exports OMP_NUM_THREADS=1 to its workers)
+    lib.fn("set_num_threads")(threads or os.cpu_count() or 1)
     cores = lib.fn("num_threads")()
     with oracle.sim(cfg, openmp=True) as o:
         o.set_agents(pos, np.zeros_like(pos), par)
@@ -287,7 +320,7 @@ def main():
         ds.step(W)
         ds.shard.sim.enable_timers(True)
         launches0 = ds.shard.sim.launch_count()
-        sampler = ClockSampler(list(range(min(world, ndev))), enabled=rank == 0)
+        sampler = ClockSampler(device)
         sampler.start()
         barrier()
         lib.check(lib.fn("sim_timer_start")(ds.shard.sim.h))
