@@ -62,6 +62,9 @@ def test_no_cpu_fallback_without_gpu():
     agents = crm.generate_agents(2, crm.AgentSettings(), crm.Configuration())
     with pytest.raises(crm.SimulationError):
         crm.run_simulation_with_agents(crm.Configuration(t_max=1.0), agents)
+    # page-locked buffers come from the CUDA runtime: no device, no silent pageable stand-in
+    with pytest.raises(MemoryError):
+        lib.pinned_empty((4, 8, 3), "float32")
 
 
 def test_product_package_does_not_import_oracle():
