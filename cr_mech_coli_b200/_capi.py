@@ -158,6 +158,8 @@ class Library:
             "sim_timer_stop": (C.c_int, [vp, P(C.c_double)]),
             "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
             "sim_set_skin": (C.c_int, [vp, C.c_float]),
+            "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
+            "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
             "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),
@@ -204,6 +206,8 @@ class Library:
             "sim_pairs_in_cutoff": (u64, [vp]),
             "num_threads": (C.c_int, []),
             "set_num_threads": (None, [C.c_int]),
+            "set_mie_textbook": (None, [C.c_int]),
+            "sim_set_pair_once": (C.c_int, [vp, C.c_int]),
         }
         for name, (res, args) in sig.items():
             if self.has(name):
@@ -333,6 +337,13 @@ class Sim:
 
     def set_exact_math(self, exact: bool):
         self.L.check(self.L.fn("sim_set_exact_math")(self.h, int(exact)))
+
+    def set_solver_order(self, stored_increments: int):
+        """History depth of the Adams-Bashforth solver: 0 Euler, 1 AB2, 2 AB3 (before set_agents)."""
+        self.L.check(self.L.fn("sim_set_solver_order")(self.h, int(stored_increments)))
+
+    def set_spring_end_weight(self, w: float):
+        self.L.check(self.L.fn("sim_set_spring_end_weight")(self.h, float(w)))
 
     def set_skin(self, skin: float):
         self.L.check(self.L.fn("sim_set_skin")(self.h, float(skin)))

@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const float y2 = rcp_refined(n2);
     const float u2[3] = {div_rn(c2[0], n2, y2), div_rn(c2[1], n2, y2), div_rn(c2[2], n2, y2)};
     if (l < NV - 1 && n2 != 0.0f) {
-        float k = tension * (n2 - L);
+        float k = (tension * (n2 - L)) * d.spring_w;
 #pragma unroll
         for (int c = 0; c < 3; ++c) fs[c] = -u2[c] * k;
     }
@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         }
         if (amp != 0.0f) {
             float n0, n1;
-            normal_pair(d.seed, d.iteration, a, (uint64_t)(l * 3 + c), n0, n1);
+            normal_pair(d.seed, d.iteration, d.rkey ? d.rkey[a] : a, (uint64_t)(l * 3 + c), n0, n1);
             ip += amp * n0;
         }
         Pnew[c] = P[c] + ip;
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     if (l == 0 && valid && !keep) {
         gs.z = newL;
         d.grow[a] = gs;
-        if (nh < 2) d.nhist[a] = (uint8_t)(nh + 1);
+        if (nh < d.ab_hist) d.nhist[a] = (uint8_t)(nh + 1);
     }
 }
 
@@ -564,10 +564,11 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
         const float L = gs.z;
         const float div_factor = __fsub_rn(0.5f, __fdiv_rn(pot.radius, __fmul_rn((float)NV, L)));
         const float newL = __fmul_rn(div_factor, L);
-        const float g1 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 0, d.seed, d.iteration, a, 0);
-        const float g2 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 1, d.seed, d.iteration, a, 0);
-        const float l1 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 0, d.seed, d.iteration, a, 1);
-        const float l2 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 1, d.seed, d.iteration, a, 1);
+        const uint64_t key = d.rkey ? d.rkey[a] : a;  // the mother's global slot
+        const float g1 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 0, d.seed, d.iteration, key, 0);
+        const float g2 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 1, d.seed, d.iteration, key, 0);
+        const float l1 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 0, d.seed, d.iteration, key, 1);
+        const float l2 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 1, d.seed, d.iteration, key, 1);
         d.grow[a] = make_float4(g1, l1, newL, 0.f);
         d.grow[b] = make_float4(g2, l2, newL, 0.f);
         d.pot[b] = pot;

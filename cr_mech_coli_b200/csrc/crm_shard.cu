@@ -193,7 +193,9 @@ int crm_sim_set_global_slots(crm_sim* s, const uint64_t* gslots, uint32_t n) {
         s->gslot[a] = gslots[a];
         if (s->ids[a].kind == CRM_ID_INITIAL) s->ids[a].counter = gslots[a];  // Initial(index in the input list)
     }
-    return 0;
+    CK(cudaSetDevice(s->device));
+    s->rkey_on = true;
+    return crm_upload_rkeys(s, 0, n);
 }
 
 uint32_t crm_sim_halo_record_bytes(const crm_sim* s) { return (uint32_t)(s->lp + 5) * 16u; }
@@ -523,6 +525,10 @@ int crm_sim_migrate_out(crm_sim* s, void* host_lo, uint32_t cap_lo, uint32_t* n_
     s->need_rebuild = true;
     s->have_lists = false;
     s->d.n = s->d.n_own = n_new;
+    {
+        int rc = crm_upload_rkeys(s, 0, n_new);
+        if (rc) return rc;
+    }
     // bounds (vertex records, spheres, chords) of the moved slots
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     launch_bounds_kernel(s->nv, s->d, s->stream);
@@ -569,6 +575,7 @@ int crm_sim_migrate_in(crm_sim* s, const void* host_buf, uint32_t n_in) {
     s->launches += 1;
     CK(cudaGetLastError());
     s->n = n0 + n_in;
+    if ((rc = crm_upload_rkeys(s, n0, n_in))) return rc;
     s->n_ghost = 0;
     s->need_rebuild = true;
     s->have_lists = false;

@@ -73,6 +73,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.cyc, on, (size_t)cap);
     G(s->d.nn, on, (size_t)cap);
     G(s->tile_buf, on, (size_t)cap);
+    G(s->rkey_buf, on, (size_t)cap);
     G(s->d.bsphere, on, (size_t)cap);
     G(s->d.chord, 2 * on, (size_t)2 * cap);
     G(s->d.vrec, on * s->lp, (size_t)cap * s->lp);
@@ -107,7 +108,19 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     for (void* q : retired) CK(cudaFree(q));
     s->d.divcap = cap;
     s->d.tile = s->sim_of.empty() ? nullptr : s->tile_buf;
+    s->d.rkey = s->rkey_on ? s->rkey_buf : nullptr;
     s->cap = cap;
+    return 0;
+}
+
+// device copy of the global slots [first, first + count): the key of the rods' random streams
+int crm_upload_rkeys(crm_sim* s, uint32_t first, uint32_t count) {
+    if (!s->rkey_on || !count) return 0;
+    std::vector<uint32_t> k(count);
+    for (uint32_t i = 0; i < count; ++i) k[i] = (uint32_t)s->gslot[first + i];
+    CK(cudaMemcpyAsync(s->rkey_buf + first, k.data(), sizeof(uint32_t) * count, cudaMemcpyHostToDevice, s->stream));
+    CK(cudaStreamSynchronize(s->stream));  // (k is a temporary)
+    s->d.rkey = s->rkey_buf;
     return 0;
 }
 
@@ -318,6 +331,7 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
         if (!s->sim_of.empty()) s->sim_of.push_back(s->sim_of[a]);  // b == sim_of.size(): slots are appended in order
     }
     s->n = n0 + n_div;
+    if ((rc = crm_upload_rkeys(s, n0, n_div))) return rc;
     s->n_ghost = 0;  // the new cells took the first ghost slots; ghosts are re-sent every step
     s->d.n = s->d.n_own = s->n;
     s->bounds_fresh = false;
@@ -666,6 +680,10 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     s->d.slab_lo = -INFINITY;
     s->d.slab_hi = INFINITY;
     s->d.seed = c->rng_seed;
+    s->d.ab_hist = 2;
+    s->d.spring_w = 1.0f;
+    if (const char* so = getenv("CRM_B200_SOLVER_ORDER")) s->d.ab_hist = std::min(2, std::max(0, atoi(so)));
+    if (const char* sw = getenv("CRM_B200_SPRING_END_WEIGHT")) s->d.spring_w = (float)atof(sw);
     *out = s;
     return 0;
 }
@@ -675,7 +693,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.gof, s->d.dcnt, s->d.dextra, s->d.dmark, s->d.dsib, s->d.dirty_list, s->d.dirty_n, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage, s->stage2, s->rkey_buf};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
@@ -711,6 +729,22 @@ int crm_sim_set_patching(crm_sim* s, int on) {
     return 0;
 }
 
+// Open restatement decisions as run-time parameters (the same switches exist in the oracle).
+// stored_increments: 0 Euler, 1 Adams-Bashforth 2, 2 Adams-Bashforth 3 (cellular_raza's
+// `mechanics_solver_order` kwarg of run_main!, not passed at reference src/simulation.rs:283-292).
+int crm_sim_set_solver_order(crm_sim* s, int stored_increments) {
+    if (!s || stored_increments < 0 || stored_increments > 2) return fail(CRM_ERR_INVALID, "stored increments must be 0, 1 or 2");
+    if (s->n) return fail(CRM_ERR_INVALID, "set the solver order before the agents");
+    s->d.ab_hist = stored_increments;
+    return 0;
+}
+// weight of the spring force on each end of a segment: 1 (docs/source/model.rst:32-36) or 1/2
+int crm_sim_set_spring_end_weight(crm_sim* s, float w) {
+    if (!s || !(w > 0.0f)) return fail(CRM_ERR_INVALID, "spring end weight must be > 0");
+    s->d.spring_w = w;
+    return 0;
+}
+
 int crm_sim_set_exact_math(crm_sim* s, int exact) {
     s->fast_math = !exact;
     return 0;
@@ -741,6 +775,8 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->n_sims = 1;
     s->d.tile = nullptr;
     s->d.sim_fail = nullptr;
+    s->rkey_on = false;
+    s->d.rkey = nullptr;
     s->vox_counter.assign((size_t)s->cfg.n_voxels[0] * s->cfg.n_voxels[1], 0);
     const size_t m = (size_t)n * nv * 3;
     if (n) {
@@ -846,7 +882,8 @@ int crm_sim_set_agents_batched(crm_sim* s, const float* pos, const float* vel, c
     if (n) CK(cudaMemcpyAsync(s->tile_buf, sim_of, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     s->d.tile = s->tile_buf;
-    return 0;
+    s->rkey_on = true;  // a member draws the numbers of its stand-alone run (key = slot inside the member)
+    return crm_upload_rkeys(s, 0, n);
 }
 
 // Error isolation of batched sims: a BoundaryError / CalcError stops only the sim it happens in
@@ -936,9 +973,13 @@ int crm_sim_run_costs(crm_sim* s, const float* targets, uint32_t n_results, uint
         cudaFree(d_cost);
         cudaFree(d_start);
     };
-    CK(cudaMalloc(&d_target, sizeof(float) * per_result * std::max(1u, n_results)));
-    CK(cudaMalloc(&d_cost, sizeof(float) * s->n_sims));
-    CK(cudaMalloc(&d_start, sizeof(uint32_t) * (s->n_sims + 1)));
+    if (cudaMalloc(&d_target, sizeof(float) * per_result * std::max(1u, n_results)) != cudaSuccess ||
+        cudaMalloc(&d_cost, sizeof(float) * s->n_sims) != cudaSuccess ||
+        cudaMalloc(&d_start, sizeof(uint32_t) * (s->n_sims + 1)) != cudaSuccess) {
+        cleanup();
+        cudaGetLastError();
+        return fail(CRM_ERR_NOMEM, "cost evaluation: out of device memory");
+    }
     cudaMemcpyAsync(d_target, targets, sizeof(float) * per_result * n_results, cudaMemcpyHostToDevice, s->stream);
     cudaMemcpyAsync(d_start, start.data(), sizeof(uint32_t) * (s->n_sims + 1), cudaMemcpyHostToDevice, s->stream);
     cudaMemsetAsync(d_cost, 0, sizeof(float) * s->n_sims, s->stream);

@@ -112,6 +112,8 @@ struct crm_sim {
     std::vector<uint32_t> sim_of;        // batched sims: sim index per slot (empty: one colony)
     uint32_t n_sims = 1;
     uint32_t* tile_buf = nullptr;        // device copy of sim_of (Dev::tile points here when batched)
+    uint32_t* rkey_buf = nullptr;        // device copy of gslot (Dev::rkey points here when gslot != slot)
+    bool rkey_on = false;                // sharded / batched runs: random streams are keyed by the global slot
     std::vector<uint64_t> sim_rods;      // batched sims: rods ever created per sim (next local slot)
     std::vector<uint32_t> sim_rods0;     // batched sims: rods at set_agents (a sim that divided has more now)
     int* sim_fail = nullptr;             // device [n_sims], Dev::sim_fail points here while isolation is on
@@ -150,4 +152,5 @@ void crm_fill_device_params(const crm_rod_params& p, crm::PotParams& pot, crm::M
                             crm::CycleParams& cyc);
 int crm_reserve(crm_sim* s, uint32_t need);
 int crm_read_status(crm_sim* s);
+int crm_upload_rkeys(crm_sim* s, uint32_t first, uint32_t count);
 int crm_report_device_error(crm_sim* s);

@@ -194,6 +194,16 @@ int crm_sim_compute_forces(crm_sim* sim, float* out_force, uint32_t* out_n_neigh
  * approximations (rsqrt/ex2/lg2/rcp).  Env CRM_B200_EXACT_MATH=1 sets the default. */
 int crm_sim_set_exact_math(crm_sim* sim, int exact);
 
+/* Two decisions the un-vendored cellular_raza source would settle, as run-time
+ * parameters; the oracle has the same switches.  Both must precede crm_sim_set_agents.
+ * stored_increments: history depth of the Adams-Bashforth mechanics solver, 0 Euler, 1 AB2,
+ * 2 AB3 (default; cellular_raza's `mechanics_solver_order` kwarg of run_main!, which reference
+ * src/simulation.rs:283-292 does not pass).  Env CRM_B200_SOLVER_ORDER sets the default. */
+int crm_sim_set_solver_order(crm_sim* sim, int stored_increments);
+/* Weight of a segment's spring force on each of its two ends: 1 (default, reference
+ * docs/source/model.rst:32-36) or 1/2.  Env CRM_B200_SPRING_END_WEIGHT sets the default. */
+int crm_sim_set_spring_end_weight(crm_sim* sim, float weight);
+
 /* Skin (um) of the persistent neighbour structure: rods and point-segment evaluations within
  * range + skin are listed once and reused until a vertex has moved more than skin/2 (Verlet
  * lists; results are identical because skipped evaluations are exact zeros).  0 = search from

@@ -77,6 +77,15 @@ typedef struct oracle_sim {
     snapshot* snaps;
     uint32_t n_snaps;
     uint64_t pairs_in_cutoff;
+    /* open restatement decisions as run-time switches (same in the CUDA path) */
+    int ab_hist;       /* stored increments of the Adams-Bashforth solver: 0 Euler, 1 AB2, 2 AB3 */
+    float spring_w;    /* weight of a segment's spring force on each end: 1 or 1/2 */
+    int mie_textbook;  /* 1: Mie constant with the textbook exponent m/(n-m) (probe only) */
+    int pair_once;     /* 1: compute_forces evaluates each unordered pair once and scatters to both rods
+                          (the reference backend's schedule; timing path of bench.py) */
+    float* scratch;    /* pair_once: per-thread force accumulators */
+    int scratch_threads;
+    uint32_t scratch_cap;
     char err[512];
 } oracle_sim;
 
@@ -153,6 +162,7 @@ static int build_schedule(const crm_config* c, uint64_t** out, uint32_t* n_out, 
  * Mie: V(x)=strength*C*((sigma/x)^n-(sigma/x)^m), sigma=(m/n)^(1/(n-m))*r,
  * C=n/(n-m)*(n/m)^(n/(n-m)), repulsive magnitude clamped by `bound`, zero beyond
  * cutoff (reference cr_mech_coli/crm_fit/plotting.py:285-309). */
+static int g_mie_textbook = 0; /* probe switch (oracle_set_mie_textbook): SURVEY 9.4 */
 static inline void point_force(const crm_rod_params* own, float ext_radius, const float p[3],
                                const float q[3], float f[3]) {
     float zx = p[0] - q[0], zy = p[1] - q[1], zz = p[2] - q[2];
@@ -169,7 +179,7 @@ static inline void point_force(const crm_rod_params* own, float ext_radius, cons
         float R = own->radius + ext_radius;
         float en = own->en, em = own->em;
         float sigma = R * powf(em / en, 1.0f / (en - em));
-        float C = en / (en - em) * powf(en / em, en / (en - em));
+        float C = en / (en - em) * powf(en / em, (g_mie_textbook ? em : en) / (en - em));
         float part = en / sigma * powf(sigma / r, en + 1.0f) - em / sigma * powf(sigma / r, em + 1.0f);
         float fm = fminf(own->strength * C * part, own->bound);
         float co = (r > own->cutoff) ? 0.0f : 1.0f;
@@ -341,6 +351,99 @@ static void compute_forces(oracle_sim* s, int count_pairs) {
     if (count_pairs) s->pairs_in_cutoff = pairs;
 }
 
+/* The same forces with the reference backend's schedule: every unordered pair of the
+ * 3x3 voxel stencil is visited once, calculate_force_between is called for (A,B) and for (B,A), and
+ * the four half-weighted results are scattered to both rods.  Half the point-segment evaluations of
+ * the gather form above; the f32 summation order differs (per-thread accumulators are reduced at the
+ * end), so this is the TIMING path of bench.py's CPU baseline, the gather form stays the checker. */
+static void compute_forces_pair_once(oracle_sim* s) {
+    const uint32_t nv = s->nv;
+    const size_t m = (size_t)nv * 3;
+    const int nx = (int)s->cfg.n_voxels[0], ny = (int)s->cfg.n_voxels[1];
+    sort_into_voxels(s);
+    int nt = 1;
+#ifdef _OPENMP
+    nt = omp_get_max_threads();
+#endif
+    if (s->scratch_threads != nt || s->scratch_cap < s->n) {
+        free(s->scratch);
+        s->scratch = (float*)malloc(sizeof(float) * (size_t)nt * s->n * m);
+        s->scratch_threads = nt;
+        s->scratch_cap = s->n;
+    }
+    uint32_t* counts = (uint32_t*)calloc((size_t)nt * s->n, sizeof(uint32_t));
+#ifdef _OPENMP
+#pragma omp parallel
+#endif
+    {
+        int tid = 0;
+#ifdef _OPENMP
+        tid = omp_get_thread_num();
+#endif
+        float* acc = s->scratch + (size_t)tid * s->n * m;
+        uint32_t* cnt = counts + (size_t)tid * s->n;
+        memset(acc, 0, sizeof(float) * (size_t)s->n * m);
+        float fo[3 * 64], fe[3 * 64], fo2[3 * 64], fe2[3 * 64];
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 16)
+#endif
+        for (int64_t a = 0; a < (int64_t)s->n; ++a) {
+            const float* A = s->pos + (size_t)a * m;
+            const crm_rod_params* pa = &s->par[a];
+            int vx = (int)(s->vox_of[a] / (uint32_t)ny), vy = (int)(s->vox_of[a] % (uint32_t)ny);
+            for (int ix = vx - 1; ix <= vx + 1; ++ix) {
+                if (ix < 0 || ix >= nx) continue;
+                for (int iy = vy - 1; iy <= vy + 1; ++iy) {
+                    if (iy < 0 || iy >= ny) continue;
+                    uint32_t v = (uint32_t)(ix * ny + iy);
+                    for (uint32_t k = s->vox_start[v]; k < s->vox_start[v + 1]; ++k) {
+                        uint32_t b = s->vox_items[k];
+                        if (b <= (uint32_t)a) continue; /* each unordered pair once */
+                        const float* B = s->pos + (size_t)b * m;
+                        const crm_rod_params* pb = &s->par[b];
+                        rod_force_between(pa, nv, A, B, pb->radius, fo, fe);
+                        rod_force_between(pb, nv, B, A, pa->radius, fo2, fe2);
+                        float* FA = acc + (size_t)a * m;
+                        float* FB = acc + (size_t)b * m;
+                        for (uint32_t t = 0; t < m; ++t) {
+                            FA[t] += 0.5f * fo[t] + 0.5f * fe2[t];
+                            FB[t] += 0.5f * fe[t] + 0.5f * fo2[t];
+                        }
+                        const uint32_t sn = (uint32_t)senses(nv, A, B, pa->radius, pb->radius); /* symmetric */
+                        cnt[a] += sn;
+                        cnt[b] += sn;
+                    }
+                }
+            }
+        }
+#ifdef _OPENMP
+#pragma omp for schedule(static)
+#endif
+        for (int64_t a = 0; a < (int64_t)s->n; ++a) {
+            float* F = s->force + (size_t)a * m;
+            const float* A = s->pos + (size_t)a * m;
+            const float* V = s->vel + (size_t)a * m;
+            uint32_t c = 0;
+            memset(F, 0, sizeof(float) * m);
+            for (int t = 0; t < nt; ++t) {
+                const float* src = s->scratch + ((size_t)t * s->n + a) * m;
+                for (uint32_t q = 0; q < m; ++q) F[q] += src[q];
+                c += counts[(size_t)t * s->n + a];
+            }
+            s->par[a].n_neighbors = c;
+            for (uint32_t i = 0; i < nv; ++i) {
+                F[3 * i + 2] -= s->cfg.gel_pressure;
+                if (s->cfg.surface_friction != 0.0f && A[3 * i + 2] <= s->cfg.surface_friction_distance) {
+                    F[3 * i + 0] -= s->cfg.surface_friction * V[3 * i + 0];
+                    F[3 * i + 1] -= s->cfg.surface_friction * V[3 * i + 1];
+                    F[3 * i + 2] -= s->cfg.surface_friction * V[3 * i + 2];
+                }
+            }
+        }
+    }
+    free(counts);
+}
+
 /* RodMechanics::calculate_increment (reference docs/source/model.rst:28-57;
  * delegation witnessed at src/crm_amir.rs:88-91): springs between consecutive
  * vertices, restoring bending force eta*(pi-alpha) on interior vertices with
@@ -356,7 +459,7 @@ static void increment(const oracle_sim* s, uint32_t a, float* dv) {
         float c[3] = {P[3 * i] - P[3 * i + 3], P[3 * i + 1] - P[3 * i + 4], P[3 * i + 2] - P[3 * i + 5]};
         float len = sqrtf(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
         if (len != 0.0f) {
-            float k = p->spring_tension * (len - p->spring_length);
+            float k = (p->spring_tension * (len - p->spring_length)) * s->spring_w;
             for (int d = 0; d < 3; ++d) {
                 float f = -(c[d] / len) * k;
                 dv[3 * i + d] += f;
@@ -436,7 +539,7 @@ static void integrate(oracle_sim* s, uint32_t a, const float* dv) {
         P[t] += ip;
         V[t] += iv;
     }
-    if (s->nhist[a] < 2) s->nhist[a]++;
+    if (s->nhist[a] < s->ab_hist) s->nhist[a]++;
 }
 
 /* Cycle::update_cycle (reference src/agent.rs:573-595). */
@@ -635,7 +738,8 @@ static int apply_boundary(oracle_sim* s) {
 static int step_once(oracle_sim* s) {
     s->iteration += 1;
     s->rod_steps += s->n;
-    compute_forces(s, 0);
+    if (s->pair_once) compute_forces_pair_once(s);
+    else compute_forces(s, 0);
     float dv[3 * 64];
     for (uint32_t a = 0; a < s->n; ++a) {
         increment(s, a, dv);
@@ -686,6 +790,8 @@ ORACLE_API int oracle_sim_create(const crm_config* c, int device, oracle_sim** o
     (void)device;
     oracle_sim* s = (oracle_sim*)calloc(1, sizeof(oracle_sim));
     s->cfg = *c;
+    s->ab_hist = 2;
+    s->spring_w = 1.0f;
     if (c->n_voxels[0] == 0 || c->n_voxels[1] == 0 || !(c->domain_size[0] > 0) || !(c->domain_size[1] > 0) ||
         !(c->domain_height > 0)) {
         snprintf(g_err, sizeof(g_err), "invalid domain configuration");
@@ -711,6 +817,7 @@ ORACLE_API void oracle_sim_destroy(oracle_sim* s) {
     free(s->pos); free(s->vel); free(s->force); free(s->dx1); free(s->dv1); free(s->dx2); free(s->dv2);
     free(s->nhist); free(s->par); free(s->id); free(s->parent); free(s->div_flag); free(s->vox_of);
     free(s->vox_items); free(s->vox_counter); free(s->vox_start); free(s->save_iter);
+    free(s->scratch);
     free(s);
 }
 
@@ -767,6 +874,26 @@ ORACLE_API int oracle_sim_compute_forces(oracle_sim* s, float* out_force, uint32
     if (out_force) memcpy(out_force, s->force, sizeof(float) * (size_t)s->n * s->nv * 3);
     if (out_nn)
         for (uint32_t a = 0; a < s->n; ++a) out_nn[a] = s->par[a].n_neighbors;
+    return 0;
+}
+
+/* switches for the open restatement decisions and the timing schedule */
+ORACLE_API int oracle_sim_set_solver_order(oracle_sim* s, int stored_increments) {
+    if (stored_increments < 0 || stored_increments > 2) return CRM_ERR_INVALID;
+    s->ab_hist = stored_increments;
+    return 0;
+}
+ORACLE_API int oracle_sim_set_spring_end_weight(oracle_sim* s, float w) {
+    s->spring_w = w;
+    return 0;
+}
+ORACLE_API void oracle_set_mie_textbook(int on) { g_mie_textbook = on; }
+ORACLE_API int oracle_sim_set_pair_once(oracle_sim* s, int on) {
+    s->pair_once = on;
+    return 0;
+}
+ORACLE_API int oracle_sim_last_forces(oracle_sim* s, float* out_force) {
+    memcpy(out_force, s->force, sizeof(float) * (size_t)s->n * s->nv * 3);
     return 0;
 }
 
