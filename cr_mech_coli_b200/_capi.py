@@ -146,6 +146,7 @@ class Library:
             # product only
             "abi_version": (C.c_int, []),
             "device_count": (C.c_int, []),
+            "device_mem_info": (C.c_int, [C.c_int, P(C.c_size_t), P(C.c_size_t)]),
             "counter_to_color": (None, [u32, P(C.c_uint8 * 3)]),
             "color_to_counter": (u32, [P(C.c_uint8 * 3)]),
             "generate_positions": (
@@ -208,6 +209,7 @@ class Library:
             "set_num_threads": (None, [C.c_int]),
             "set_mie_textbook": (None, [C.c_int]),
             "sim_set_pair_once": (C.c_int, [vp, C.c_int]),
+            "sim_force_abs_sum": (C.c_int, [vp, vp]),
         }
         for name, (res, args) in sig.items():
             if self.has(name):

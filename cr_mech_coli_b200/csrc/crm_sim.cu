@@ -428,7 +428,7 @@ static int launch_force_from_lists(crm_sim* s) {
     return 0;
 }
 
-// [n_div, reason to rebuild] of the step just enqueued, for the sharded coordinator's all_gather
+// [n_div, reason to rebuild, error code, 0] of the step just enqueued, for the sharded coordinator's all_gather
 // (the same conditions step_finish evaluates on the host)
 __global__ void k_status_flags(const Status* st, float skin, uint32_t host_want, uint32_t* flags) {
     const float disp = sqrtf(__uint_as_float(st->disp2_bits));
@@ -436,6 +436,8 @@ __global__ void k_status_flags(const Status* st, float skin, uint32_t host_want,
     if (skin > 0.0f) want |= (st->plist_overflow != 0) | !(disp < 0.4999f * skin);
     flags[0] = st->n_div;
     flags[1] = want ? 1u : 0u;
+    flags[2] = (uint32_t)(-st->err_code);  // 0 | -CRM_ERR_BOUNDARY | -CRM_ERR_NUMERIC: every slab learns of the error
+    flags[3] = 0u;
 }
 
 // A step is enqueued (step_enqueue: nothing waits for the device unless a search needs fresh bounds)
@@ -452,7 +454,7 @@ static int step_enqueue(crm_sim* s, uint32_t* dev_flags) {
 static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     if (s->n == 0) {
         s->iteration += 1;
-        if (dev_flags) CK(cudaMemsetAsync(dev_flags, 0, 2 * sizeof(uint32_t), s->stream));
+        if (dev_flags) CK(cudaMemsetAsync(dev_flags, 0, 4 * sizeof(uint32_t), s->stream));
         return 0;
     }
     s->iteration += 1;
@@ -622,6 +624,15 @@ int crm_device_count(void) {
         return -1;
     }
     return n;
+}
+
+int crm_device_mem_info(int device, size_t* free_bytes, size_t* total_bytes) {
+    CK(cudaSetDevice(device));
+    size_t f = 0, t = 0;
+    CK(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return 0;
 }
 
 int crm_save_schedule(const crm_config* config, uint64_t* out, uint32_t cap, uint64_t* n_iterations) {

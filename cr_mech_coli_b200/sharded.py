@@ -161,7 +161,7 @@ class Shard:
         # cannot outlive it): transport enqueued under it is ordered with the kernels
         self.stream = torch.cuda.Stream(device=self.device)
         lib.check(lib.fn("sim_set_stream")(self.sim.h, C.c_void_p(self.stream.cuda_stream)))
-        self.flags = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.flags = torch.zeros(4, dtype=torch.int32, device=self.device)  # [divisions, rebuild wish, -error, 0]
         self.n_send = [0, 0]
         self.n_recv = [0, 0]
 
@@ -438,7 +438,7 @@ class LocalCluster:
             s.step_begin()
         status = [s.step_end() for s in self.shards]
         for s, st in zip(self.shards, status):  # the device-written flags are what the ranks all_gather
-            assert s.flags.tolist() == [st[0], int(bool(st[1]))], (s.flags.tolist(), st)
+            assert s.flags.tolist()[:3] == [st[0], int(bool(st[1])), 0], (s.flags.tolist(), st)
         self.moved = False
         return status
 
@@ -611,8 +611,8 @@ class DistributedShard:
         [divisions, rebuild] flags -> one host wait."""
         s, t = self.shard, self.tr.torch
         if self._flags_all is None:
-            self._flags_all = t.zeros(2 * self.world, dtype=t.int32, device=s.device)
-            self._flags_host = t.zeros(2 * self.world, dtype=t.int32).pin_memory()
+            self._flags_all = t.zeros(4 * self.world, dtype=t.int32, device=s.device)
+            self._flags_host = t.zeros(4 * self.world, dtype=t.int32).pin_memory()
             self._flags_event = t.cuda.Event()
         with t.cuda.stream(s.stream):
             if not self._halo_ahead:
@@ -630,12 +630,31 @@ class DistributedShard:
         # the host waits for the flags only: the exchange above is still running when the next step's
         # kernels are enqueued behind it, so the device never waits for the host
         self._flags_event.synchronize()
+        st = self._flags_host.numpy().reshape(self.world, 4).astype(np.float64)
+        if st[:, 2].max() > 0:  # a BoundaryError / CalcError in some slab ends the run in ALL slabs
+            s.stream.synchronize()
+            self._halo_ahead = False
+            self._raise_collective(st[:, 2])
         s.step_end()
         self.moved = False
-        st = self._flags_host.numpy().reshape(self.world, 2).astype(np.float64)
         if st[:, 1].max() > 0 or st[:, 0].sum() > 0:
             s.stream.synchronize()  # the synchronous rebuild / division protocol follows: drain the stream first
         return st
+
+    def _raise_collective(self, codes, own: Exception | None = None):
+        """Every rank raises the SimulationError of the run (the reference reports one error for the whole
+        simulation, src/simulation.rs:237): the owner of the failing rod with the position dump, the
+        others naming the rank."""
+        if own is None and codes[self.rank] > 0:
+            try:
+                self.shard.step_end()
+            except _capi.SimulationError as e:
+                own = e
+        if own is not None:
+            raise own
+        r = int(np.argmax(codes > 0))
+        kind = _capi.STATUS_NAMES.get(-int(codes[r]), f"error {-int(codes[r])}")
+        raise _capi.SimulationError(f"{kind}: raised in slab {r} at iteration {self.iteration + 1}")
 
     def _frozen_halo(self):
         s = self.shard
@@ -663,13 +682,19 @@ class DistributedShard:
             else:
                 self._halo_ahead = False
                 self._exchange_halos()
-                n_div, want = self.shard.step_local()
-                self.iteration += 1
-                if not (self.can_divide or self.use_lists):
-                    continue  # nothing to agree on: every step searches afresh
+                own, code = None, 0
+                try:
+                    n_div, want = self.shard.step_local()
+                except _capi.SimulationError as e:  # the other slabs must learn of it before anyone raises
+                    own, n_div, want = e, 0, 1
+                    code = next((-k for k, v in _capi.STATUS_NAMES.items() if str(e).startswith(v)), 1)
                 # one small all_gather per step: divisions need the lists of all slabs for the
-                # identifiers, and the persistent neighbour structure is rebuilt in all slabs at once
-                st = self.tr.allgather([n_div, int(want or self.moved)])
+                # identifiers, the persistent neighbour structure is rebuilt in all slabs at once, and
+                # an error in one slab ends the run in all of them
+                st = self.tr.allgather([n_div, int(want or self.moved), code])
+                if st[:, 2].max() > 0:
+                    self._raise_collective(st[:, 2], own)
+                self.iteration += 1
             self.rebuild_next = bool(st[:, 1].max() > 0) or not self.use_lists
             if st[:, 0].sum() > 0:
                 gs, vx = self.shard.pending_divisions()

@@ -114,6 +114,9 @@ int crm_abi_version(void);
 const char* crm_last_error(void);
 /* Number of visible CUDA devices (<0: CUDA unavailable). */
 int crm_device_count(void);
+/* Free / total device memory in bytes (leak checks of callers that open a sim per cost evaluation,
+ * reference src/crm_fit/predict.rs:231-287). */
+int crm_device_mem_info(int device, size_t* free_bytes, size_t* total_bytes);
 
 /* ---- host helpers on the boundary ------------------------------------ */
 /* Replaces `counter_to_color` / `color_to_counter` (reference src/imaging.rs:28-66). */
@@ -309,8 +312,8 @@ int crm_sim_set_ghosts_msgs(crm_sim* sim, const void* dev_msg_lo, const void* de
  * device; the caller's transport must be ordered on crm_sim_stream (a cudaStream_t).
  *   crm_sim_halo_repack     the frozen selections packed again into the two messages
  *   crm_sim_ghosts_refresh  received records scattered to the ghost slots of the last rebuild step
- *   crm_sim_step_begin      the step enqueued; dev_flags[0..1] = {divisions, reason to rebuild}
- *                           written on the stream (device memory, may be NULL)
+ *   crm_sim_step_begin      the step enqueued; dev_flags[0..3] = {divisions, reason to rebuild, -error code
+ *                           (0: none), 0} written on the stream (device memory, 16 bytes, may be NULL)
  *   crm_sim_step_end        one wait + the host part of the step.  It waits for the step's own work (an event
  *                           behind its status read-back), not for what the caller enqueued on the stream after
  *                           crm_sim_step_begin: the next halo exchange keeps running while the host decides

@@ -83,6 +83,7 @@ typedef struct oracle_sim {
     int mie_textbook;  /* 1: Mie constant with the textbook exponent m/(n-m) (probe only) */
     int pair_once;     /* 1: compute_forces evaluates each unordered pair once and scatters to both rods
                           (the reference backend's schedule; timing path of bench.py) */
+    float* force_abs;  /* [n][nv][3] sum of |half-weighted pair contributions| per component (tolerance scale) */
     float* scratch;    /* pair_once: per-thread force accumulators */
     int scratch_threads;
     uint32_t scratch_cap;
@@ -310,6 +311,8 @@ static void compute_forces(oracle_sim* s, int count_pairs) {
         const float* A = s->pos + (size_t)a * nv * 3;
         const crm_rod_params* pa = &s->par[a];
         memset(F, 0, sizeof(float) * nv * 3);
+        float* FA = s->force_abs ? s->force_abs + (size_t)a * nv * 3 : NULL;
+        if (FA) memset(FA, 0, sizeof(float) * nv * 3);
         uint32_t count = 0;
         int vx = (int)(s->vox_of[a] / (uint32_t)ny), vy = (int)(s->vox_of[a] % (uint32_t)ny);
         for (int ix = vx - 1; ix <= vx + 1; ++ix) {
@@ -327,6 +330,7 @@ static void compute_forces(oracle_sim* s, int count_pairs) {
                     for (uint32_t t = 0; t < nv * 3; ++t) {
                         F[t] += 0.5f * fo[t];
                         F[t] += 0.5f * fe2[t];
+                        if (FA) FA[t] += 0.5f * fabsf(fo[t]) + 0.5f * fabsf(fe2[t]);
                     }
                     count += (uint32_t)senses(nv, A, B, pa->radius, pb->radius);
                     if (count_pairs) pairs += (uint64_t)within_cutoff(nv, A, B, pa->cutoff);
@@ -894,6 +898,18 @@ ORACLE_API int oracle_sim_set_pair_once(oracle_sim* s, int on) {
 }
 ORACLE_API int oracle_sim_last_forces(oracle_sim* s, float* out_force) {
     memcpy(out_force, s->force, sizeof(float) * (size_t)s->n * s->nv * 3);
+    return 0;
+}
+
+/* Per component: sum of the absolute values of the half-weighted pair contributions that make up the
+ * interaction force of the current state (the scale of the f32 summation noise of that component). */
+ORACLE_API int oracle_sim_force_abs_sum(oracle_sim* s, float* out) {
+    size_t m = (size_t)s->n * s->nv * 3;
+    s->force_abs = (float*)malloc(sizeof(float) * (m ? m : 1));
+    compute_forces(s, 0);
+    memcpy(out, s->force_abs, sizeof(float) * m);
+    free(s->force_abs);
+    s->force_abs = NULL;
     return 0;
 }
 

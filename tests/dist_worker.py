@@ -44,6 +44,28 @@ def main():
         print(f"dist_worker ok: world {world}, final rods {len(snaps[-1][1])}")
     dist.barrier()
     ds.close()
+
+    # a model error in ONE slab must end the run in ALL slabs (the reference reports one SimulationError,
+    # src/simulation.rs:237), not leave the others waiting in a collective: a rod of the last slab flies out
+    cfg2 = _capi.make_config(domain_size=(L, L), n_voxels=(3, 3), t_max=5.0, dt=0.1, n_saves=0)
+    par2 = morse_params(n, growth_rate=0.0)
+    par2["spring_length_threshold"] = 1e30
+    vel2 = np.zeros_like(pos)
+    far = int(np.argmax(pos[:, :, 0].mean(axis=1)))
+    vel2[far, :, 0] = 1e4
+    ds2 = sharded.DistributedShard(lib, cfg2, sharded.SlabPartition.uniform(L, world), local)
+    ds2.set_agents(pos, vel2, par2)
+    try:
+        ds2.step(30)
+        raised = None
+    except _capi.SimulationError as e:
+        raised = str(e)
+    assert raised is not None and "BoundaryError" in raised, raised
+    owner = world - 1
+    assert ("Particle is out of domain" in raised) == (rank == owner), (rank, raised)
+    print(f"dist_worker error propagation ok on rank {rank}: {raised[:60]}")
+    dist.barrier()
+    ds2.close()
     dist.destroy_process_group()
 
 

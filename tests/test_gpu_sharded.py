@@ -177,3 +177,39 @@ def test_sharded_persistent_lists(product_lib):
     assert (ids == idg).all()
     assert np.abs(ps - pg).max() < 1e-3
     cl.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_stochastic_run_is_partition_independent(product_lib, world):
+    """Wiener term and Normal setters are keyed by the GLOBAL slot (the slot a rod has in the unsharded run), so a
+    sharded stochastic run draws exactly the numbers of the oracle: lineage bit-exact, positions 1e-3 um."""
+    n, L = 48, 420.0
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(3, 3), t_max=16.0, dt=0.1, n_saves=7, rng_seed=11)
+    pos = lattice_colony(n, spacing=(50.0, 40.0), margin=40.0, seed=12, angle_std=0.5)
+    par = morse_params(n, growth_rate=0.08, diffusion_constant=0.02)
+    rng = np.random.default_rng(5)
+    par["growth_rate"] = rng.uniform(0.06, 0.1, n)
+    par["growth_setter_kind"] = _capi.SETTER_NORMAL
+    par["growth_setter_a"] = 0.08
+    par["growth_setter_b"] = 0.015
+    par["threshold_setter_kind"] = _capi.SETTER_NORMAL
+    par["threshold_setter_a"] = 6.0
+    par["threshold_setter_b"] = 0.4
+    par["spring_length"] = rng.uniform(2.5, 3.5, n)
+    vel = np.zeros_like(pos)
+    cl = sharded.LocalCluster(product_lib, cfg, sharded.SlabPartition.uniform(L, world))
+    cl.set_agents(pos, vel, par)
+    ss = cl.run()
+    with oracle.sim(cfg) as o:
+        o.set_agents(pos, vel, par)
+        o.run()
+        so = o.snapshots()
+    assert len(ss) == len(so) == 9
+    for (it, ps, vs, pars, ids, prs), (_, po, vo, paro, ido, pro) in zip(ss, so):
+        assert ps.shape == po.shape, f"rod count differs at iteration {it}"
+        assert (ids == ido).all() and (prs == pro).all(), f"lineage differs at iteration {it}"
+        np.testing.assert_allclose(pars["growth_rate"], paro["growth_rate"], rtol=2e-6)
+        np.testing.assert_allclose(pars["spring_length_threshold"], paro["spring_length_threshold"], rtol=2e-6)
+        assert np.abs(ps - po).max() < 1e-3, f"iteration {it}: {np.abs(ps - po).max()}"
+    assert len(ss[-1][1]) > n
+    cl.close()

@@ -167,3 +167,60 @@ def test_colors_match_reference_formula():
         c = (counter * 157 * 163 * 173) % 251**3
         assert tuple(rgb) == (c // 251**2, (c % 251**2) // 251, c % 251)
         assert lib.lib.oracle_color_to_counter(C.byref(rgb)) == counter
+
+
+def test_pair_once_schedule_equals_gather_form(oracle_lib):
+    """The timing schedule of bench.py's CPU arm (each unordered pair visited once, four half-weighted results
+    scattered to both rods: the reference backend's schedule) gives the gather form's forces up to
+    f32 summation order, and the same neighbour counts and trajectory."""
+    from cr_mech_coli_b200.testing import lattice_colony, lattice_domain, mie_params
+    from oracle import oracle
+
+    n = 400
+    L = lattice_domain(n)
+    cfg = _capi.make_config(domain_size=(L, L), n_voxels=(max(1, int(L // 40)),) * 2, dt=0.01)
+    pos = lattice_colony(n, seed=9)
+    par = mie_params(n)
+    outs = []
+    for once in (0, 1):
+        with oracle.sim(cfg, openmp=True) as o:
+            o.L.check(o.L.fn("sim_set_pair_once")(o.h, once))
+            o.set_agents(pos, np.zeros_like(pos), par)
+            o.step(5)
+            f = np.zeros_like(pos)
+            o.L.check(o.L.fn("sim_last_forces")(o.h, f.ctypes.data))
+            outs.append((f, o.get_state()))
+    (f0, s0), (f1, s1) = outs
+    assert np.abs(f0).max() > 0
+    assert np.abs(f1 - f0).max() < 2e-6 * np.abs(f0).max()
+    assert (s0[2]["n_neighbors"] == s1[2]["n_neighbors"]).all()
+    assert np.abs(s0[0] - s1[0]).max() < 1e-5
+
+
+def test_solver_order_switch(oracle_lib):
+    """Euler / AB2 / AB3 on a single stretched rod: all contract the rod, pairwise different at O(dt^2)."""
+    from cr_mech_coli_b200.testing import morse_params
+    from oracle import oracle
+
+    cfg = _capi.make_config(dt=0.1, t_max=5.0)
+    pos = np.zeros((1, 8, 3), np.float32)
+    pos[0, :, 0] = 30 + 3.5 * np.arange(8)
+    pos[0, :, 1] = 50
+    pos[0, :, 2] = 1.25
+    par = morse_params(1, growth_rate=0.0)
+    ends = []
+    for order in (0, 1, 2):
+        with oracle.sim(cfg) as o:
+            o.L.check(o.L.fn("sim_set_solver_order")(o.h, order))
+            o.set_agents(pos, np.zeros_like(pos), par)
+            o.step(20)
+            ends.append(o.get_state()[0])
+    length = [float(p[0, -1, 0] - p[0, 0, 0]) for p in ends]
+    assert all(l < 24.5 for l in length)
+    assert abs(length[0] - length[1]) > 1e-4 and abs(length[1] - length[2]) > 1e-5
+    with oracle.sim(cfg) as o:  # half the spring force per end: slower contraction
+        o.L.check(o.L.fn("sim_set_spring_end_weight")(o.h, 0.5))
+        o.set_agents(pos, np.zeros_like(pos), par)
+        o.step(20)
+        half = o.get_state()[0]
+    assert float(half[0, -1, 0] - half[0, 0, 0]) > length[2] + 1e-3
