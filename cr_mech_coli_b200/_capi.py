@@ -159,6 +159,8 @@ class Library:
             "sim_timer_stop": (C.c_int, [vp, P(C.c_double)]),
             "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
             "sim_set_skin": (C.c_int, [vp, C.c_float]),
+            "sim_set_batching": (C.c_int, [vp, C.c_int]),
+            "sim_read_step_stats": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u32)]),
             "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
             "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
             "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
@@ -201,6 +203,11 @@ class Library:
             "sim_apply_divisions": (C.c_int, [vp, vp, vp, vp, u32]),
             "sim_take_snapshot": (C.c_int, [vp]),
             "sim_snapshot_global_slots": (C.c_int, [vp, u32, vp]),
+            "polygon_hulls": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, vp, vp, u32]),
+            "render_mask_2d": (C.c_int, [vp, vp, vp, u32, u32, P(C.c_float * 2), P(u32 * 2), C.c_float, C.c_float, vp,
+                                         vp, P(C.c_double)]),
+            "overlap": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, P(C.c_float)]),
+            "parents_diff_mask": (C.c_int, [vp, vp, u64, vp, u32, vp, u32, C.c_float, vp, P(C.c_int64)]),
             "host_alloc": (vp, [C.c_size_t]),
             "host_free": (None, [vp]),
             # oracle only
@@ -346,6 +353,16 @@ class Sim:
 
     def set_spring_end_weight(self, w: float):
         self.L.check(self.L.fn("sim_set_spring_end_weight")(self.h, float(w)))
+
+    def set_batching(self, on: bool):
+        """List steps in batches with a device-side latch (default) or one host round trip per step."""
+        self.L.check(self.L.fn("sim_set_batching")(self.h, int(on)))
+
+    def step_stats(self):
+        ms, nl, nb, bl = C.c_double(0), C.c_uint64(0), C.c_uint64(0), C.c_uint32(0)
+        self.L.check(self.L.fn("sim_read_step_stats")(self.h, C.byref(ms), C.byref(nl), C.byref(nb), C.byref(bl)))
+        return {"integrate_ms": float(ms.value), "integrate_launches": int(nl.value), "batches": int(nb.value),
+                "batch_len": int(bl.value)}
 
     def set_skin(self, skin: float):
         self.L.check(self.L.fn("sim_set_skin")(self.h, float(skin)))

@@ -48,8 +48,11 @@ class _Snapshot:
         return RodAgent._from_record(self.pos[k], self.vel[k], self.par[k])
 
     def as_dict(self):
+        """Ordered like the reference's BTreeMap<CellIdentifier, _> (Division < Initial < Inserted): callers
+        that stack ``.values()`` into arrays see the reference's row order."""
         idents, parents = self.idents()
-        return {i: (self.agent(k), p) for k, (i, p) in enumerate(zip(idents, parents))}
+        order = sorted(range(len(idents)), key=lambda k: idents[k])
+        return {idents[k]: (self.agent(k), parents[k]) for k in order}
 
 
 class CellContainer:
@@ -213,6 +216,11 @@ class CellContainer:
 
     @staticmethod
     def load_from_storage(config, path):
-        raise NotImplementedError(
-            "load_from_storage reads cellular_raza's on-disk SerdeJson store; only StorageOption.Memory is "
-            "implemented on this path (SURVEY.md §8f-2)")
+        """reference src/cell_container.rs:322-359: the save points below ``path`` (the directory above
+        ``cells``) as a container.  Reads the records ``run_simulation_with_agents`` writes under
+        ``StorageOption.SerdeJson`` (this repo's JSON schema, see storage.py; cellular_raza's own files are
+        rejected with a ValueError)."""
+        from . import storage
+        from pathlib import Path
+
+        return CellContainer(path=Path(path), _snapshots=[_Snapshot(*s) for s in storage.read_snapshots(path)])

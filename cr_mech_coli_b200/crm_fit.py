@@ -396,11 +396,15 @@ def _is_normal(x) -> np.ndarray:
     return np.isfinite(x) & (np.abs(x) >= np.finfo(np.float32).tiny)
 
 
-def predict_calculate_cost_population(parameters, positions_all, iterations, settings: Settings, device: int = 0):
+def predict_calculate_cost_population(parameters, positions_all, iterations, settings: Settings, device: int = 0,
+                                      return_status: bool = False):
     """Costs of a whole population ``parameters[M, D]`` in ONE batched device run (the unit scipy's
     differential evolution evaluates per generation with ``updating='deferred'``; the reference fans
     ``predict_calculate_cost`` out over processes, src/crm_fit/optimize.rs:75-95,235-252).  Per member:
-    simulation error or non-normal cost -> ``constants.error_cost`` (predict.rs:224-228,249-256)."""
+    simulation error or non-normal cost -> ``constants.error_cost`` (predict.rs:224-228,249-256).  A member
+    whose cells divide also gets ``error_cost`` here (population extension: the other members' costs stay
+    usable); the reference's single-vector call raises for it, and so does ``predict_calculate_cost`` below.
+    ``return_status=True`` adds the per-member status (0 | ERR_BOUNDARY | ERR_NUMERIC | ERR_DIVISION)."""
     positions_all = np.asarray(positions_all, dtype=np.float32)
     if positions_all.ndim != 4:
         raise ValueError("positions_all must be (n_results, n_agents, n_vertices, 2 or 3)")
@@ -408,13 +412,18 @@ def predict_calculate_cost_population(parameters, positions_all, iterations, set
     pos, vel, par, sim_of = define_initial_agents_packed(parameters, positions_all[0], settings.domain_height,
                                                          settings.parameters, c)
     M = int(sim_of[-1]) + 1 if len(sim_of) else 0
-    costs, _ = costs_on_device(_capi.product(), settings.to_config()._to_c(), pos, vel, par, sim_of, M, positions_all,
-                               iterations, device, error_cost=c.error_cost)
+    costs, status = costs_on_device(_capi.product(), settings.to_config()._to_c(), pos, vel, par, sim_of, M,
+                                    positions_all, iterations, device, error_cost=c.error_cost)
     costs[~_is_normal(costs)] = c.error_cost
-    return costs
+    return (costs, status) if return_status else costs
 
 
 def predict_calculate_cost(parameters, positions_all, iterations, settings: Settings, device: int = 0) -> float:
-    """``crm_fit.predict_calculate_cost`` (predict.rs:202-229) for one parameter vector."""
-    return float(predict_calculate_cost_population(np.asarray(parameters, np.float32)[None, :], positions_all,
-                                                   iterations, settings, device)[0])
+    """``crm_fit.predict_calculate_cost`` (predict.rs:202-229) for one parameter vector.  A division raises
+    IndexError like the reference (predict.rs:271-280 propagates it through ``?``); BoundaryError / CalcError and
+    non-normal costs give ``constants.error_cost``."""
+    costs, status = predict_calculate_cost_population(np.asarray(parameters, np.float32)[None, :], positions_all,
+                                                      iterations, settings, device, return_status=True)
+    if int(status[0]) == _capi.ERR_DIVISION:
+        raise IndexError("Cell division is currently not supported by this optimization algorithm")
+    return float(costs[0])

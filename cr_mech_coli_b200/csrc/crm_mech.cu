@@ -195,6 +195,11 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const size_t o = (size_t)a * STRIDE;
     const bool hv = valid && l < NV;
     const int li = l < NV ? l : 0;
+    {   // a step of a batch behind the one that latched (blocks of the latching step itself read their own
+        // iteration or 0 and go on)
+        const unsigned stop = *(volatile const unsigned*)&d.status->stop_iter;
+        if (stop != 0u && stop < (unsigned)d.iteration) return;
+    }
 
     float P[3], V[3], F[3];
 #pragma unroll
@@ -354,6 +359,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         if (!finite || !inside) {
             if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
                 d.status->err_slot = a;
+            d.status->stop_iter = (unsigned)d.iteration;
         }
     }
     if (d.vbuild) {  // displacement since the persistent neighbour structure was built
@@ -364,7 +370,11 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             e2 = e * e;
         }
         const float dd = group_max<LP>(hv ? e2 : 0.0f, gm);
-        if (l == 0 && valid) atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
+        if (l == 0 && valid) {
+            atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
+            // the host's rule (step_conclude): the lists serve while every vertex stays within skin/2
+            if (!(sqrtf(dd) < 0.4999f * d.skin)) d.status->stop_iter = (unsigned)d.iteration;
+        }
     }
     // The bounds of the search (sphere, chord, cull thresholds) are recomputed by k_bounds only when a
     // search follows (rebuild steps); every step needs just the vertex record of the force kernel.
@@ -389,6 +399,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             ix = min(max(ix, 0), d.unx - 1);
             iy = min(max(iy, 0), d.uny - 1);
             unsigned k = atomicAdd(&d.status->n_div, 1u);
+            d.status->stop_iter = (unsigned)d.iteration;
             if (k < d.divcap) {
                 d.divlist[k].slot = a;
                 d.divlist[k].uvox = (uint32_t)(ix * d.uny + iy);
@@ -413,8 +424,8 @@ __device__ __forceinline__ float setter_sample(int kind, float a, float b, int w
     if (kind == CRM_SETTER_EXPLICIT) return which == 0 ? a : b;
     if (b == 0.0f) return a;
     float n0, n1;
-    normal_pair(seed ^ 0xD1B54A32D192ED03ULL, it, slot, stream, n0, n1);
-    return a + b * (which == 0 ? n0 : n1);
+    normal_pair_precise(seed ^ 0xD1B54A32D192ED03ULL, it, slot, stream, n0, n1);
+    return __fadd_rn(a, __fmul_rn(b, which == 0 ? n0 : n1));
 }
 
 template <int NV>

@@ -508,21 +508,10 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     return 0;
 }
 
-static int step_finish(crm_sim* s) {
-    if (!s->step_open) return 0;
-    s->step_open = false;
-    if (s->n == 0) return 0;
+// host half of a step (or of a batch of list steps) once its status block has arrived
+static int step_conclude(crm_sim* s) {
     int rc;
-    // the step's own work only: what a caller enqueued behind it on the stream (the sharded coordinator's
-    // next halo exchange) keeps running while the host decides what the next step is
-    CK(cudaEventSynchronize(s->ev_status));
     crm_note_list_flags(s);
-    if (s->timers) {
-        float ms = 0.0f;
-        CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-        s->force_ms += ms;
-        s->force_launches += 1;
-    }
     if ((rc = crm_report_device_error(s))) return rc;
     const uint32_t n_div = s->h_status->n_div;
     bool want = s->h_status->n_leave > 0;
@@ -553,9 +542,100 @@ static int step_finish(crm_sim* s) {
     return 0;
 }
 
+static int step_finish(crm_sim* s) {
+    if (!s->step_open) return 0;
+    s->step_open = false;
+    if (s->n == 0) return 0;
+    // the step's own work only: what a caller enqueued behind it on the stream (the sharded coordinator's
+    // next halo exchange) keeps running while the host decides what the next step is
+    CK(cudaEventSynchronize(s->ev_status));
+    if (s->timers) {
+        float ms = 0.0f;
+        CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        s->force_ms += ms;
+        s->force_launches += 1;
+    }
+    return step_conclude(s);
+}
+
+// ---- the host out of the step loop -----------------------------------------------------------------
+// Between two searches nothing the host decides depends on a step's outcome unless that step divides a rod,
+// fails, or moves a vertex beyond skin/2.  Up to `n_max` list steps are therefore enqueued back to back
+// (k_force_eval + k_integrate each, no host wait); the first step after which the host has to act latches
+// its iteration on the device (Status::stop_iter), the kernels of the steps behind it return at once, and ONE
+// status block comes back per batch.  The accumulators of the block (max displacement, division list, error)
+// are only ever written by the latching step, so they read exactly as after a single step.  Results are
+// identical to stepping one by one: the same kernels see the same state.
+static bool batchable(const crm_sim* s) {
+    return s->batching && persistent(s) && !s->need_rebuild && s->have_lists && s->n_dirty == 0 && !s->sharded && s->n > 0 &&
+           s->pending_div == 0 && !s->step_open;
+}
+
+static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
+    const uint64_t it0 = s->iteration;
+    const uint32_t B = std::max<uint32_t>(1u, std::min<uint32_t>(n_max, s->batch_len));
+    s->d.n = s->n + s->n_ghost;
+    s->d.n_own = s->n;
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    const bool uniform = !s->lists_slow;
+    const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
+    for (uint32_t k = 0; k < B; ++k) {
+        s->d.iteration = it0 + k + 1;
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
+        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, s->stream);
+        if (s->timers && k == 0) {
+            CK(cudaEventRecord(s->ev1, s->stream));
+            CK(cudaEventRecord(s->ev2, s->stream));
+        }
+        launch_integrate(s->nv, s->d, s->stream);
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
+    }
+    s->launches += 2ull * B;
+    s->bounds_fresh = false;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaEventRecord(s->ev_status, s->stream));
+    CK(cudaEventSynchronize(s->ev_status));
+    const uint32_t stop = s->h_status->stop_iter;
+    const uint32_t n_done = stop ? (uint32_t)(stop - (uint32_t)it0) : B;
+    if (n_done == 0 || n_done > B) return fail(CRM_ERR_CUDA, "batched steps: latch out of range (%u of %u)", n_done, B);
+    s->iteration = it0 + n_done;
+    s->d.iteration = s->iteration;
+    s->rod_steps += (uint64_t)s->n * n_done;
+    s->n_eval_steps += n_done;
+    s->evals_since_build += n_done;
+    s->steps_since_build += n_done;
+    s->n_batches += 1;
+    s->batch_len = stop ? std::max<uint32_t>(1u, n_done) : std::min<uint32_t>(2u * B, 64u);
+    if (s->timers) {
+        float ms = 0.0f;
+        CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        s->force_ms += ms;
+        s->force_launches += 1;
+        CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+        s->integrate_ms += ms;
+        s->integrate_launches += 1;
+    }
+    *done = n_done;
+    return step_conclude(s);
+}
+
 static int step_once(crm_sim* s) {
     const int rc = step_enqueue(s, nullptr);
     return rc ? rc : step_finish(s);
+}
+
+// n_steps steps: batches of list steps where nothing needs the host, single steps otherwise
+static int advance(crm_sim* s, uint64_t n_steps) {
+    while (n_steps) {
+        uint32_t done = 1;
+        int rc;
+        if (batchable(s)) rc = step_batch(s, (uint32_t)std::min<uint64_t>(n_steps, 1u << 20), &done);
+        else rc = step_once(s);
+        if (rc) return rc;
+        n_steps -= done;
+    }
+    return 0;
 }
 
 static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
@@ -676,7 +756,10 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaMallocHost(&s->h_status, sizeof(Status) + 128));  // + pinned scratch (message headers)
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
+    CK(cudaEventCreate(&s->ev2));
+    CK(cudaEventCreate(&s->ev3));
     CK(cudaEventCreateWithFlags(&s->ev_status, cudaEventDisableTiming));
+    if (const char* bt = getenv("CRM_B200_BATCH")) s->batching = bt[0] != '0';
     s->d.lx = c->domain_size[0];
     s->d.ly = c->domain_size[1];
     s->d.lz = c->domain_height;
@@ -710,6 +793,8 @@ void crm_sim_destroy(crm_sim* s) {
     if (s->h_status) cudaFreeHost(s->h_status);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev2) cudaEventDestroy(s->ev2);
+    if (s->ev3) cudaEventDestroy(s->ev3);
     if (s->ev_status) cudaEventDestroy(s->ev_status);
     if (s->ev_t0) cudaEventDestroy(s->ev_t0);
     if (s->ev_t1) cudaEventDestroy(s->ev_t1);
@@ -1005,7 +1090,9 @@ int crm_sim_run_costs(crm_sim* s, const float* targets, uint32_t n_results, uint
     };
     accumulate();
     while (s->iteration < s->max_iter) {  // to t_max like the reference: a late error still costs the member
-        if ((rc = step_once(s))) {
+        while (next < n_results && result_iterations[next] <= s->iteration) next++;
+        const uint64_t target = next < n_results ? std::min<uint64_t>(result_iterations[next], s->max_iter) : s->max_iter;
+        if ((rc = advance(s, std::max<uint64_t>(1, target - s->iteration)))) {
             cleanup();
             return rc;
         }
@@ -1033,11 +1120,7 @@ int crm_sim_snapshot_sim_index(const crm_sim* s, uint32_t k, uint32_t* out) {
 
 int crm_sim_step(crm_sim* s, uint32_t n_steps) {
     CK(cudaSetDevice(s->device));
-    for (uint32_t k = 0; k < n_steps; ++k) {
-        int rc = step_once(s);
-        if (rc) return rc;
-    }
-    return 0;
+    return advance(s, n_steps);
 }
 
 // The step in two halves for callers that order their own work (halo transport, collectives) on
@@ -1076,8 +1159,7 @@ int crm_sim_step_timed(crm_sim* s, uint32_t n_steps, double* ms_out) {
     CK(cudaEventCreate(&a));
     CK(cudaEventCreate(&b));
     CK(cudaEventRecord(a, s->stream));
-    int rc = 0;
-    for (uint32_t k = 0; k < n_steps && !rc; ++k) rc = step_once(s);
+    const int rc = advance(s, n_steps);
     CK(cudaEventRecord(b, s->stream));
     CK(cudaEventSynchronize(b));
     float ms = 0.0f;
@@ -1121,7 +1203,9 @@ int crm_sim_run(crm_sim* s) {
         next++;
     }
     while (s->iteration < s->max_iter) {
-        if ((rc = step_once(s))) return rc;
+        // to the next save point (or the end) in as few host round trips as the colony allows
+        const uint64_t target = next < s->save_iter.size() ? std::min(s->save_iter[next], s->max_iter) : s->max_iter;
+        if ((rc = advance(s, std::max<uint64_t>(1, target - s->iteration)))) return rc;
         while (next < s->save_iter.size() && s->save_iter[next] < s->iteration) next++;
         if (next < s->save_iter.size() && s->save_iter[next] == s->iteration) {
             if ((rc = crm_take_snapshot(s))) return rc;
@@ -1215,6 +1299,27 @@ int crm_sim_enable_timers(crm_sim* s, int enable) {
     s->timers = enable != 0;
     s->force_ms = 0.0;
     s->force_launches = 0;
+    s->integrate_ms = 0.0;
+    s->integrate_launches = 0;
+    return 0;
+}
+
+// Integrator launches timed next to the force launches (first step of every batch), and how the steps were
+// driven: batches of list steps (one status read-back each) vs single steps.
+int crm_sim_read_step_stats(crm_sim* s, double* integrate_ms, uint64_t* integrate_launches, uint64_t* n_batches,
+                            uint32_t* batch_len) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    if (integrate_ms) *integrate_ms = s->integrate_ms;
+    if (integrate_launches) *integrate_launches = s->integrate_launches;
+    if (n_batches) *n_batches = s->n_batches;
+    if (batch_len) *batch_len = s->batch_len;
+    return 0;
+}
+
+// 1 (default): list steps are enqueued in batches with a device-side latch; 0: one host round trip per step.
+int crm_sim_set_batching(crm_sim* s, int on) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    s->batching = on != 0;
     return 0;
 }
 

@@ -137,6 +137,13 @@ struct crm_sim {
     // timers
     bool timers = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev2 = nullptr, ev3 = nullptr;  // around the integrator launch of the first step of a batch
+    double integrate_ms = 0.0;
+    uint64_t integrate_launches = 0;
+    // batches of list steps (crm_sim.cu step_batch)
+    bool batching = true;      // CRM_B200_BATCH=0 / crm_sim_set_batching: one host round trip per step
+    uint32_t batch_len = 4;    // steps of the next batch: doubles after a full batch (<= 64), shrinks to what a latched one served
+    uint64_t n_batches = 0;
     cudaEvent_t ev_status = nullptr;  // recorded behind the status read-back of a step: what step_finish waits for
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // crm_sim_timer_start / stop
     double force_ms = 0.0;

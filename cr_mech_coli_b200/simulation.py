@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-from . import _capi
+from . import _capi, storage
 from .cell_container import CellContainer, _Snapshot
 from .datatypes import AgentSettings, Configuration, PhysicalInteraction, RodAgent, StorageOption
 
@@ -66,9 +66,7 @@ def pack_agents(agents):
 def run_simulation_with_agents(config: Configuration, agents, device: int = 0) -> CellContainer:
     """reference src/simulation.rs:232-319.  Agents are copied in, the whole run executes on the GPU
     (``crm_sim_run``), snapshots come back at the save points as packed arrays."""
-    unsupported = [o for o in config.storage_options if o != StorageOption.Memory]
-    if unsupported:
-        raise NotImplementedError(f"storage options {unsupported} are not implemented (Memory only)")
+    storage.check_options(config.storage_options)
     agents = list(agents)
     lib = _capi.product()
     pos, vel, par = pack_agents(agents)
@@ -82,7 +80,14 @@ def run_simulation_with_agents(config: Configuration, agents, device: int = 0) -
             e = np.zeros((0, 8, 3), np.float32)
             snaps = [_Snapshot(int(i), e, e, np.zeros(0, _capi.ROD_PARAMS_DTYPE), np.zeros(0, _capi.IDENT_DTYPE),
                                np.zeros(0, _capi.IDENT_DTYPE)) for i in its]
-    return CellContainer(path=None, _snapshots=snaps)
+    # StorageOption.SerdeJson: every save point also goes to disk; the container remembers where
+    # (reference src/simulation.rs:221-230,307-316)
+    path = None
+    if StorageOption.SerdeJson in config.storage_options:
+        path = storage.new_run_directory(config)
+        for s in snaps:
+            storage.write_snapshot(path, s.iteration, s.pos, s.vel, s.par, s.ids, s.parents)
+    return CellContainer(path=path, _snapshots=snaps)
 
 
 def run_simulations_batched(config: Configuration, agent_lists, device: int = 0):
@@ -90,9 +95,7 @@ def run_simulations_batched(config: Configuration, agent_lists, device: int = 0)
     (parameter-fitting ensembles: reference src/crm_fit/predict.rs:231-287 run once per parameter
     point by src/crm_fit/optimize.rs:75-95).  Returns one ``CellContainer`` per agent list, equal to
     what the individual calls return (deterministic settings)."""
-    unsupported = [o for o in config.storage_options if o != StorageOption.Memory]
-    if unsupported:
-        raise NotImplementedError(f"storage options {unsupported} are not implemented (Memory only)")
+    storage.check_options(config.storage_options)
     agent_lists = [list(a) for a in agent_lists]
     n_sims = len(agent_lists)
     flat = [a for lst in agent_lists for a in lst]

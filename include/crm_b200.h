@@ -207,6 +207,16 @@ int crm_sim_set_solver_order(crm_sim* sim, int stored_increments);
  * docs/source/model.rst:32-36) or 1/2.  Env CRM_B200_SPRING_END_WEIGHT sets the default. */
 int crm_sim_set_spring_end_weight(crm_sim* sim, float weight);
 
+/* How the steps are driven.  Between two searches a step needs the host only if it divides a rod, fails or moves
+ * a vertex beyond skin/2; crm_sim_step / _run / _run_costs therefore enqueue list steps in batches (the first
+ * such step latches on the device, later steps of the batch return at once) and read ONE status block per
+ * batch.  Results equal one-by-one stepping.  crm_sim_set_batching(0) / env CRM_B200_BATCH=0 restores one host
+ * round trip per step.  crm_sim_read_step_stats: integrator time next to crm_sim_read_timers' force time (both
+ * sampled on the first step of every batch), batches run, current batch length. */
+int crm_sim_set_batching(crm_sim* sim, int on);
+int crm_sim_read_step_stats(crm_sim* sim, double* integrate_ms, uint64_t* integrate_launches, uint64_t* n_batches,
+                            uint32_t* batch_len);
+
 /* Skin (um) of the persistent neighbour structure: rods and point-segment evaluations within
  * range + skin are listed once and reused until a vertex has moved more than skin/2 (Verlet
  * lists; results are identical because skipped evaluations are exact zeros).  0 = search from
@@ -347,6 +357,31 @@ int crm_sim_snapshot_global_slots(const crm_sim* sim, uint32_t k, uint64_t* out)
  * MEASURED_PEAKS.json): dense FP32 FMA TFLOP/s, MUFU.EX2 Top/s, and the SM clock the FMA
  * figure implies at 128 lanes/SM/clk. */
 int crm_microbench(int device, double* fp32_tflops, double* mufu_tops, double* sm_mhz_est);
+
+/* ---- 2-D mask path: the step after the mechanics in the crm_divide objective ------------
+ * Host buffers in and out; kernels in csrc/crm_raster.cu.  No graphics API is involved. */
+/* Replaces `calculate_polygon_hull` (reference src/fitting.rs:514-620): the capsule-chain outline of each of
+ * the n rods (pos [n][n_vertices][3], xy used).  out_xy [n][cap][2], out_count [n]. */
+int crm_polygon_hulls(const float* pos, const float* radii, uint32_t n, uint32_t n_vertices, float delta_angle,
+                      float epsilon, float* out_xy, uint32_t* out_count, uint32_t cap);
+/* Replaces `render_mask_2d` (reference src/fitting.rs:121-244): rods in draw order (the reference iterates a
+ * BTreeMap over CellIdentifier) with their colours [n][3] -> instance-colour bitmap and overlap bitmap,
+ * both [resolution[1]][resolution[0]][3] u8, row 0 = largest y.  kernel_ms (may be NULL) receives the
+ * device time of the kernels. */
+int crm_render_mask_2d(const float* pos, const float* radii, const uint8_t* colors, uint32_t n, uint32_t n_vertices,
+                       const float domain_size[2], const uint32_t resolution[2], float delta_angle, float epsilon,
+                       uint8_t* out_mask, uint8_t* out_overlap, double* kernel_ms);
+/* Replaces `overlap` (reference src/fitting.rs:299-345): summed intersection area of all pairs of outlines. */
+int crm_overlap(const float* pos, const float* radii, uint32_t n, uint32_t n_vertices, float delta_angle, float epsilon,
+                float* out_area);
+/* Replaces `parents_diff_mask` (reference src/fitting.rs:42-109): 0 where the masks agree, parent_penalty where
+ * one cell is the parent of the other, 1 otherwise.  Colours are decoded with color_to_counter
+ * (src/imaging.rs:42-66): cell_of_counter[k] = index of the cell coloured counter_to_color(k) or -1;
+ * parent_of[cell] = index of its parent or -1.  *missing_pixel = first pixel whose colour is unknown (the
+ * reference raises KeyError) or -1. */
+int crm_parents_diff_mask(const uint8_t* mask1, const uint8_t* mask2, uint64_t n_pixels, const int32_t* cell_of_counter,
+                          uint32_t n_counters, const int32_t* parent_of, uint32_t n_cells, float parent_penalty,
+                          float* out, int64_t* missing_pixel);
 
 #ifdef __cplusplus
 }

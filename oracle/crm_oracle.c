@@ -114,6 +114,18 @@ static inline void normal_pair(uint64_t seed, uint64_t a, uint64_t b, uint64_t c
     out[1] = r * sinf(ang);
 }
 
+/* the same deviates through f64 log / sin / cos rounded to f32 (division-time draws: the rounded results of
+ * glibc and of the device library agree, so drawn growth rates and thresholds are bit-identical) */
+static inline void normal_pair_precise(uint64_t seed, uint64_t a, uint64_t b, uint64_t c, float out[2]) {
+    uint64_t h = mix64(mix64(mix64(mix64(seed) ^ a) ^ b) ^ c);
+    double u1 = ((double)(uint32_t)(h >> 40) + 0.5) * (1.0 / 16777216.0);
+    double u2 = ((double)(uint32_t)((h >> 16) & 0xFFFFFFu) + 0.5) * (1.0 / 16777216.0);
+    double r = sqrt(-2.0 * log(u1));
+    double ang = 6.28318530717958647692 * u2;
+    out[0] = (float)(r * cos(ang));
+    out[1] = (float)(r * sin(ang));
+}
+
 /* ------------------------------------------------------------------------ */
 /* save schedule: reference src/simulation.rs:239-249 + cellular_raza          */
 /* FixedStepsize::from_partial_save_points (iteration = round((t - t0)/dt)).  */
@@ -628,7 +640,7 @@ static float setter_sample(int kind, float a, float b, int which, uint64_t seed,
     if (kind == CRM_SETTER_EXPLICIT) return which == 0 ? a : b;
     if (b == 0.0f) return a; /* Normal(mean, 0) */
     float nrm[2];
-    normal_pair(seed ^ 0xD1B54A32D192ED03ULL, it, slot, stream, nrm);
+    normal_pair_precise(seed ^ 0xD1B54A32D192ED03ULL, it, slot, stream, nrm);
     return a + b * nrm[which];
 }
 

@@ -98,3 +98,31 @@ def test_pinned_buffers_round_trip(product_lib):
     assert fa.tobytes() == b.last_forces().tobytes()
     with pytest.raises(ValueError):
         b.get_state(out=(out[0][: n - 1],) + out[1:])
+
+
+def test_serde_json_storage_round_trip(product_lib, tmp_path):
+    """StorageOption.SerdeJson: the run writes its save points below storage_location/<date>/cells/json/...,
+    the container remembers the run directory, and load_from_storage returns the same container
+    (reference src/simulation.rs:307-316, src/cell_container.rs:322-359; the multilayer driver's
+    load_or_compute_container, cr_mech_coli/crm_multilayer/runner.py:130-150)."""
+    import cr_mech_coli as crm_shim
+
+    config = crm_shim.Configuration(t_max=80.0, n_saves=3, storage_location=str(tmp_path / "out"),
+                                    storage_options=[crm_shim.StorageOption.Memory, crm_shim.StorageOption.SerdeJson])
+    agents = crm_shim.generate_agents(4, crm_shim.AgentSettings(), config, rng_seed=0, randomize_positions=0.1)
+    cc = crm_shim.run_simulation_with_agents(config, agents)
+    assert cc.path is not None and (cc.path / "cells" / "json").is_dir()
+    assert cc.path.parent == tmp_path / "out"
+    back = crm_shim.CellContainer.load_from_storage(config, cc.path)
+    assert back.get_all_iterations() == cc.get_all_iterations() and len(cc.get_all_iterations()) == 5
+    assert back.get_parent_map() == cc.get_parent_map() and len(cc.get_cells_at_iteration(800)) == 8
+    for it in cc.get_all_iterations():
+        a, b = cc.get_cells_at_iteration(it), back.get_cells_at_iteration(it)
+        assert list(a) == list(b)
+        for ident in a:
+            assert np.array_equal(a[ident][0].pos, b[ident][0].pos) and np.array_equal(a[ident][0].vel, b[ident][0].vel)
+            assert a[ident][0].spring_length == b[ident][0].spring_length and a[ident][1] == b[ident][1]
+    # a suffix becomes a sub-directory of the run directory
+    config.storage_suffix = "trial-7"
+    cc2 = crm_shim.run_simulation_with_agents(config, agents)
+    assert cc2.path.name == "trial-7" and (cc2.path / "cells" / "json").is_dir()

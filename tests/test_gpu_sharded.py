@@ -208,8 +208,8 @@ def test_stochastic_run_is_partition_independent(product_lib, world):
     for (it, ps, vs, pars, ids, prs), (_, po, vo, paro, ido, pro) in zip(ss, so):
         assert ps.shape == po.shape, f"rod count differs at iteration {it}"
         assert (ids == ido).all() and (prs == pro).all(), f"lineage differs at iteration {it}"
-        np.testing.assert_allclose(pars["growth_rate"], paro["growth_rate"], rtol=2e-6)
-        np.testing.assert_allclose(pars["spring_length_threshold"], paro["spring_length_threshold"], rtol=2e-6)
+        assert (pars["growth_rate"] == paro["growth_rate"]).all()
+        assert (pars["spring_length_threshold"] == paro["spring_length_threshold"]).all()
         assert np.abs(ps - po).max() < 1e-3, f"iteration {it}: {np.abs(ps - po).max()}"
     assert len(ss[-1][1]) > n
     cl.close()
