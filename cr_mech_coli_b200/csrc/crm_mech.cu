@@ -195,11 +195,8 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const size_t o = (size_t)a * STRIDE;
     const bool hv = valid && l < NV;
     const int li = l < NV ? l : 0;
-    {   // a step of a batch behind the one that latched (blocks of the latching step itself read their own
-        // iteration or 0 and go on)
-        const unsigned stop = *(volatile const unsigned*)&d.status->stop_iter;
-        if (stop != 0u && stop < (unsigned)d.iteration) return;
-    }
+    // (batches: the latch is loaded with the first wave of loads and tested behind them, see below)
+    const unsigned stop = d.latch ? *d.latch : 0u;
 
     float P[3], V[3], F[3];
 #pragma unroll
@@ -233,6 +230,9 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     const bool frozen = iso && d.sim_fail[sim_a] != 0;
     const float tension = mp.x, rigidity = mp.y, damping = mp.z, diffusion = mp.w;
     const float L = gs.z;
+    // a step of a batch behind the one that latched (blocks of the latching step itself read their own
+    // iteration or 0 and go on)
+    if (stop != 0u && stop < (unsigned)d.iteration) return;
 
     // neighbours
     float Pn[3], Pp[3];
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         if (!finite || !inside) {
             if (atomicCAS(&d.status->err_code, 0, finite ? CRM_ERR_BOUNDARY : CRM_ERR_NUMERIC) == 0)
                 d.status->err_slot = a;
-            d.status->stop_iter = (unsigned)d.iteration;
+            if (d.latch) *d.latch = (unsigned)d.iteration;
         }
     }
     if (d.vbuild) {  // displacement since the persistent neighbour structure was built
@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         if (l == 0 && valid) {
             atomicMax(&d.status->disp2_bits, __float_as_uint(dd));  // NaN compares high: forces a rebuild
             // the host's rule (step_conclude): the lists serve while every vertex stays within skin/2
-            if (!(sqrtf(dd) < 0.4999f * d.skin)) d.status->stop_iter = (unsigned)d.iteration;
+            if (d.latch && !(sqrtf(dd) < 0.4999f * d.skin)) *d.latch = (unsigned)d.iteration;
         }
     }
     // The bounds of the search (sphere, chord, cull thresholds) are recomputed by k_bounds only when a
@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
             ix = min(max(ix, 0), d.unx - 1);
             iy = min(max(iy, 0), d.uny - 1);
             unsigned k = atomicAdd(&d.status->n_div, 1u);
-            d.status->stop_iter = (unsigned)d.iteration;
+            if (d.latch) *d.latch = (unsigned)d.iteration;
             if (k < d.divcap) {
                 d.divlist[k].slot = a;
                 d.divlist[k].uvox = (uint32_t)(ix * d.uny + iy);

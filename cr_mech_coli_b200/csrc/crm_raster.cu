@@ -8,7 +8,7 @@
 // No graphics API: rasterisation is integer scanline arithmetic.  All kernels are HBM / latency bound
 // (bitmaps: 8 B of atomics + 6 B of output per pixel); nothing here is a contraction.
 // Compiled with --fmad=false: the outline arithmetic follows the reference's f32 operations one by one
-// (the only differences from the CPU oracle are the last-ulp results of cosf / sinf / atan2f).
+// and the trigonometric functions go through f64 (cos_rn): outlines equal the CPU oracle's bit for bit.
 #include "crm_sim.h"
 
 using crm::blocks_for;
@@ -19,6 +19,13 @@ constexpr int MAXV = 256;  // outline points per rod (8 vertices at delta_angle 
 constexpr float PI_F = 3.14159265358979323846f;
 
 struct P2 { float x, y; };
+
+// cos / sin / atan2 through f64, rounded to f32: the same f32 as the oracle's (glibc) on every platform, which the
+// f32 routines of libm and libdevice are not (decision R0 of oracle/raster_oracle.c).  One thread per rod, a few
+// dozen calls: the f64 rate does not matter here.
+__device__ __forceinline__ float cos_rn(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float sin_rn(float x) { return (float)sin((double)x); }
+__device__ __forceinline__ float atan2_rn(float y, float x) { return (float)atan2((double)y, (double)x); }
 
 // get_n_resolution, src/fitting.rs:403-414
 __device__ int n_resolution(float a0, float a1, float delta) {
@@ -39,7 +46,7 @@ __device__ int arc_points(P2 p, float r, float a0, float a1, float delta, F put)
     const float dangle = fabsf(end - a0) / ((float)n + 1.0f);
     for (int k = 1; k <= n; ++k) {
         const float ang = a0 + dangle * (float)k;
-        put(k - 1, P2{p.x + cosf(ang) * r, p.y + sinf(ang) * r});
+        put(k - 1, P2{p.x + cos_rn(ang) * r, p.y + sin_rn(ang) * r});
     }
     return n;
 }
@@ -56,7 +63,7 @@ __device__ void rect_points(P2 p1, P2 p2, float r, P2 c[4]) {
 }
 
 __device__ float angle_x(float dx, float dy) {  // atan2(y, x).rem_euclid(2 pi), src/fitting.rs:398-400
-    const float a = atan2f(dy, dx);
+    const float a = atan2_rn(dy, dx);
     float m = fmodf(a, 2.0f * PI_F);
     if (m < 0.0f) m += 2.0f * PI_F;
     return m;
@@ -129,7 +136,7 @@ __global__ void k_hull(const float* __restrict__ pos, const float* __restrict__ 
         rect_points(p2, p3, r, d);
         // determine_spheroid_coordinates_between_rectangles, src/fitting.rs:416-466
         const float dir1x = p2.x - p1.x, dir1y = p2.y - p1.y, dir2x = p3.x - p2.x, dir2y = p3.y - p2.y;
-        const float ang = atan2f(dir1x * dir2y - dir1y * dir2x, dir1x * dir2x + dir1y * dir2y);
+        const float ang = atan2_rn(dir1x * dir2y - dir1y * dir2x, dir1x * dir2x + dir1y * dir2y);
         const bool right = ang < 0.0f;
         float a0, a1;
         if (right) { a0 = angle_x(d[0].x - p2.x, d[0].y - p2.y); a1 = angle_x(c[1].x - p2.x, c[1].y - p2.y); }

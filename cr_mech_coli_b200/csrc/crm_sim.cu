@@ -577,6 +577,9 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
     s->d.n = s->n + s->n_ghost;
     s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    CK(cudaMemsetAsync(s->latch_buf, 0, sizeof(uint32_t), s->stream));
+    s->d.latch = s->latch_buf;
+    uint32_t* const h_latch = reinterpret_cast<uint32_t*>(s->h_status + 1) + 24;  // pinned scratch behind the status
     const bool uniform = !s->lists_slow;
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
     for (uint32_t k = 0; k < B; ++k) {
@@ -590,13 +593,15 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
         launch_integrate(s->nv, s->d, s->stream);
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
     }
+    s->d.latch = nullptr;
     s->launches += 2ull * B;
     s->bounds_fresh = false;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaMemcpyAsync(h_latch, s->latch_buf, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
     CK(cudaEventRecord(s->ev_status, s->stream));
     CK(cudaEventSynchronize(s->ev_status));
-    const uint32_t stop = s->h_status->stop_iter;
+    const uint32_t stop = *h_latch;
     const uint32_t n_done = stop ? (uint32_t)(stop - (uint32_t)it0) : B;
     if (n_done == 0 || n_done > B) return fail(CRM_ERR_CUDA, "batched steps: latch out of range (%u of %u)", n_done, B);
     s->iteration = it0 + n_done;
@@ -753,6 +758,8 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaMalloc(&s->d.status, sizeof(Status)));
     CK(cudaMemset(s->d.status, 0, sizeof(Status)));
+    CK(cudaMalloc(&s->latch_buf, 256));
+    CK(cudaMemset(s->latch_buf, 0, 256));
     CK(cudaMallocHost(&s->h_status, sizeof(Status) + 128));  // + pinned scratch (message headers)
     CK(cudaEventCreate(&s->ev0));
     CK(cudaEventCreate(&s->ev1));
@@ -787,7 +794,7 @@ void crm_sim_destroy(crm_sim* s) {
     cudaSetDevice(s->device);
     void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
                     s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.gof, s->d.dcnt, s->d.dextra, s->d.dmark, s->d.dsib, s->d.dirty_list, s->d.dirty_n, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage, s->stage2, s->rkey_buf};
+                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage, s->stage2, s->rkey_buf, s->latch_buf};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);

@@ -141,6 +141,7 @@ struct crm_sim {
     double integrate_ms = 0.0;
     uint64_t integrate_launches = 0;
     // batches of list steps (crm_sim.cu step_batch)
+    uint32_t* latch_buf = nullptr;  // device word (own cache line) the latching step writes its iteration to
     bool batching = true;      // CRM_B200_BATCH=0 / crm_sim_set_batching: one host round trip per step
     uint32_t batch_len = 4;    // steps of the next batch: doubles after a full batch (<= 64), shrinks to what a latched one served
     uint64_t n_batches = 0;

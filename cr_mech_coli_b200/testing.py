@@ -221,3 +221,34 @@ def force_errors(f_test, f_ref, f_abs_sum=None):
         big = np.linalg.norm(f_ref, axis=-1) > 1e-3 * np.linalg.norm(f_ref, axis=-1).max()
         out["vertex_rel_loaded"] = float((d[big] / np.linalg.norm(f_ref, axis=-1)[big]).max()) if big.any() else 0.0
     return out
+
+
+def multilayer_slab(n_per_rank: int, rank: int, world: int, layers: int = 3, spacing=(27.0, 6.5),
+                    layer_height: float = 5.6, z0: float = 1.5, tilt_std: float = 0.01, seed: int = 777,
+                    margin: float = 16.0):
+    """Rank ``rank``'s columns of ONE stacked colony (C4) of about ``world * n_per_rank`` rods: every layer is a
+    jittered nematic lattice, odd layers shifted by half a cell, rods slightly tilted out of the plane.
+    Returns (pos, domain (Lx, Ly), height, inner slab edges, first global slot)."""
+    sx, sy = spacing
+    per = int(np.ceil(n_per_rank / layers))
+    ny = int(np.ceil(np.sqrt(world * per * sx / sy)))
+    nxl = int(np.ceil(per / ny))
+    rng = np.random.default_rng(seed + 1000 * rank)
+    out = []
+    for k in range(layers):
+        p = lattice_colony(nxl * ny, spacing=spacing, margin=margin, seed=seed + 1 + k + 1000 * rank,
+                           z=z0 + k * layer_height, _ny=ny)
+        p[:, :, 0] += np.float32(rank * nxl * sx)
+        if k % 2:
+            p[:, :, 0] += np.float32(0.5 * sx - 0.01)
+            p[:, :, 1] += np.float32(0.5 * sy - 0.01)
+        tilt = rng.normal(0.0, tilt_std, len(p)).astype(np.float32)
+        t = p[:, :, 0] - p[:, :, 0].mean(axis=1, keepdims=True)
+        p[:, :, 2] += tilt[:, None] * t
+        out.append(p)
+    pos = np.concatenate(out).astype(np.float32)
+    domain = (float(world * nxl * sx + 2 * margin + 0.5 * sx), float(ny * sy + 2 * margin + 0.5 * sy))
+    height = float(max(20.0, z0 + layers * layer_height + 4.0))
+    # even-layer columns sit at k sx, odd-layer ones at (k + 1/2) sx: the edges lie a quarter cell below a column
+    edges = [margin + (r * nxl - 0.25) * sx for r in range(1, world)]
+    return pos, domain, height, edges, rank * len(pos)

@@ -19,6 +19,7 @@
  *       crossings) contain x; degenerate polygons (one row / one column) cover their bounding line;
  *   R3  the reference paints every pairwise intersection polygon black into the mask and white into the
  *       overlap mask AFTER all cells: restated per pixel as "covered by two or more cells";
+ *   R0  cos / sin / atan2 are evaluated in f64 and rounded to f32 (platform-independent, see cos_rn);
  *   R4  overlap(): area of the intersection of two outlines through Green's theorem over the boundary
  *       pieces of each polygon that lie inside the other (exact for simple polygons in general position).
  */
@@ -33,6 +34,14 @@
 typedef struct { float x, y; } pt;
 
 /* ---- outline ------------------------------------------------------------------------------- */
+/* Trigonometric functions through f64, rounded to f32: Rust's f32::cos / sin / atan2 call the platform libm,
+ * whose results are within an ulp but not the same on every platform (nor on the GPU).  The f64 routines of
+ * glibc and of the device library round to the same f32 (barring a 1e-9 tie), so the CUDA outline is the
+ * oracle's bit for bit; either may differ from a given libm's cosf by one ulp. */
+static float cos_rn(float x) { return (float)cos((double)x); }
+static float sin_rn(float x) { return (float)sin((double)x); }
+static float atan2_rn(float y, float x) { return (float)atan2((double)y, (double)x); }
+
 /* get_n_resolution, src/fitting.rs:403-414 */
 static int n_resolution(float a0, float a1, float delta) {
     float dangle = fabsf(a0 - a1);
@@ -52,8 +61,8 @@ static int arc_points(pt p, float r, float a0, float a1, float delta, pt* out) {
     float dangle = fabsf(end - a0) / ((float)n + 1.0f);
     for (int k = 1; k <= n; ++k) {
         float ang = a0 + dangle * (float)k;
-        out[k - 1].x = p.x + cosf(ang) * r;
-        out[k - 1].y = p.y + sinf(ang) * r;
+        out[k - 1].x = p.x + cos_rn(ang) * r;
+        out[k - 1].y = p.y + sin_rn(ang) * r;
     }
     return n;
 }
@@ -71,7 +80,7 @@ static void rect_points(pt p1, pt p2, float r, pt c[4]) {
 
 /* angle_to_x_axis: atan2(y, x).rem_euclid(2 pi), src/fitting.rs:398-400 */
 static float angle_x(float dx, float dy) {
-    float a = atan2f(dy, dx);
+    float a = atan2_rn(dy, dx);
     float m = fmodf(a, 2.0f * PI_F);
     if (m < 0.0f) m += 2.0f * PI_F;
     return m;
@@ -118,7 +127,7 @@ static int joint_points(pt p1, pt p2, pt p3, float r, float delta, pt* out, int*
     rect_points(p1, p2, r, c);
     rect_points(p2, p3, r, d);
     float dir1x = p2.x - p1.x, dir1y = p2.y - p1.y, dir2x = p3.x - p2.x, dir2y = p3.y - p2.y;
-    float ang = atan2f(dir1x * dir2y - dir1y * dir2x, dir1x * dir2x + dir1y * dir2y);
+    float ang = atan2_rn(dir1x * dir2y - dir1y * dir2x, dir1x * dir2x + dir1y * dir2y);
     *right = ang < 0.0f;
     float a0, a1;
     if (*right) { a0 = angle_x(d[0].x - p2.x, d[0].y - p2.y); a1 = angle_x(c[1].x - p2.x, c[1].y - p2.y); }
