@@ -208,6 +208,9 @@ class Library:
                                          vp, P(C.c_double)]),
             "overlap": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, P(C.c_float)]),
             "parents_diff_mask": (C.c_int, [vp, vp, u64, vp, u32, vp, u32, C.c_float, vp, P(C.c_int64)]),
+            "comm_unique_id": (C.c_int, [vp]),
+            "sim_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+            "sim_steps_sharded": (C.c_int, [vp, u32, vp, vp, vp, vp, P(u32), vp]),
             "host_alloc": (vp, [C.c_size_t]),
             "host_free": (None, [vp]),
             # oracle only

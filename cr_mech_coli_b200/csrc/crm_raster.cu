@@ -267,7 +267,13 @@ __global__ void __launch_bounds__(128) k_raster(const int2* __restrict__ hull_px
             while (b > 0 && num[b - 1] * d_ > n_ * den[b - 1]) { num[b] = num[b - 1]; den[b] = den[b - 1]; --b; }
             num[b] = n_; den[b] = d_;
         }
-        for (int k = 0; k + 1 < nc; k += 2) fill(ceil_div(num[k], den[k]), floor_div(num[k + 1], den[k + 1]));
+        // (two intervals of one outline may share their end pixel where it touches itself: covered once)
+        long long next = -(1ll << 40);
+        for (int k = 0; k + 1 < nc; k += 2) {
+            const long long xa = max(ceil_div(num[k], den[k]), next), xb = floor_div(num[k + 1], den[k + 1]);
+            fill(xa, xb);
+            next = max(next, xb + 1);
+        }
     }
 }
 

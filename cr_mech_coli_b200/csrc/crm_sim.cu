@@ -630,6 +630,22 @@ static int step_once(crm_sim* s) {
     return rc ? rc : step_finish(s);
 }
 
+// ---- the same for a slab of a sharded colony: batches of list steps INCLUDING their halo exchange -----------
+// Between two collective rebuilds a sharded step is: repack the frozen halo selections -> send/recv with the two
+// slab neighbours -> scatter the received records to the ghost slots -> k_force_eval -> k_integrate -> this
+// slab's flags {divisions, rebuild wish, error} -> all-gather of the flags.  All of it is enqueued on the sim's
+// stream from here (NCCL through crm_comm.cu), up to `n_max` steps back to back.  A one-thread kernel turns the
+// gathered flags into the latch of step_batch: the first step in which ANY slab has a reason to stop latches in
+// ALL slabs in that same step, the kernels of later steps return at once (their transfers still run, every
+// rank keeps issuing the same collectives), and the host reads one status block per batch.  No step is ever
+// computed with stale neighbour lists, so results equal the step-by-step protocol.
+__global__ void k_latch_from_flags(const uint32_t* __restrict__ flags_all, int world, uint32_t* latch, uint32_t iteration) {
+    if (threadIdx.x != 0) return;
+    uint32_t any = 0u;
+    for (int r = 0; r < world; ++r) any |= flags_all[4 * r] | flags_all[4 * r + 1] | flags_all[4 * r + 2];
+    if (any && *latch == 0u) *latch = iteration;
+}
+
 // n_steps steps: batches of list steps where nothing needs the host, single steps otherwise
 static int advance(crm_sim* s, uint64_t n_steps) {
     while (n_steps) {
@@ -798,6 +814,9 @@ void crm_sim_destroy(crm_sim* s) {
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
+    if (s->flags_host) cudaFreeHost(s->flags_host);
+    if (s->flags_dev) cudaFree(s->flags_dev);
+    if (s->comm) crm_comm_free(s->comm);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev2) cudaEventDestroy(s->ev2);
@@ -1158,6 +1177,95 @@ int crm_sim_step_end(crm_sim* s) {
     if (!s) return fail(CRM_ERR_INVALID, "null sim");
     CK(cudaSetDevice(s->device));
     return step_finish(s);
+}
+
+// Up to n_max sharded list steps with their halo exchanges (see k_latch_from_flags above).  The four buffers are the
+// caller's device message buffers of crm_sim_halo_pack_msgs / crm_sim_set_ghosts_msgs (counts as of the last
+// rebuild step).  *done = steps advanced; flags_out [4 * world] = {divisions, rebuild wish, -error, 0} of every slab
+// for the last of them.  Collective: every slab calls it with the same n_max.  A model error of THIS slab is
+// returned after flags_out has been filled, so that the caller can raise in every slab.
+int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_hi, void* recv_lo, void* recv_hi,
+                          uint32_t* done, uint32_t* flags_out) {
+    if (!s || !done || !flags_out) return fail(CRM_ERR_INVALID, "null argument");
+    if (!s->comm) return fail(CRM_ERR_INVALID, "no communicator (crm_sim_comm_init)");
+    if (!s->sharded || s->pending_div || s->step_open) return fail(CRM_ERR_INVALID, "not a slab ready to step");
+    if (!persistent(s) || !s->have_lists || s->want_rebuild || s->n_dirty)
+        return fail(CRM_ERR_INVALID, "no live neighbour structure: a collective rebuild step comes first");
+    CK(cudaSetDevice(s->device));
+    const int world = crm_comm_world(s->comm), rank = crm_comm_rank(s->comm);
+    if (!s->flags_dev) {
+        CK(cudaMalloc(&s->flags_dev, sizeof(uint32_t) * 4 * (world + 1)));
+        CK(cudaMemset(s->flags_dev, 0, sizeof(uint32_t) * 4 * (world + 1)));
+        CK(cudaMallocHost(&s->flags_host, sizeof(uint32_t) * 4 * world));
+    }
+    *done = 0;
+    if (n_max == 0) return 0;
+    s->need_rebuild = false;  // (crm_sim_keep_lists: all slabs agreed after the last step)
+    const uint64_t it0 = s->iteration;
+    const uint32_t B = std::max<uint32_t>(1u, std::min<uint32_t>(n_max, s->batch_len));
+    const size_t rb = crm_sim_halo_record_bytes(s);
+    const size_t sl = rank > 0 ? 64 + s->halo_sel_n[0] * rb : 0, sh = rank + 1 < world ? 64 + s->halo_sel_n[1] * rb : 0;
+    const size_t rl = rank > 0 ? 64 + s->ghost_n[0] * rb : 0, rh = rank + 1 < world ? 64 + s->ghost_n[1] * rb : 0;
+    if ((sl && !send_lo) || (sh && !send_hi) || (rl && !recv_lo) || (rh && !recv_hi)) return fail(CRM_ERR_INVALID, "missing message buffer");
+    s->d.n = s->n + s->n_ghost;
+    s->d.n_own = s->n;
+    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    CK(cudaMemsetAsync(s->latch_buf, 0, sizeof(uint32_t), s->stream));
+    s->d.latch = s->latch_buf;
+    uint32_t* const h_latch = reinterpret_cast<uint32_t*>(s->h_status + 1) + 24;
+    const bool uniform = !s->lists_slow;
+    const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
+    int rc = 0;
+    for (uint32_t k = 0; k < B && !rc; ++k) {
+        s->d.iteration = it0 + k + 1;
+        if ((rc = crm_sim_halo_repack(s, rank > 0 ? send_lo : nullptr, rank + 1 < world ? send_hi : nullptr))) break;
+        if ((rc = crm_comm_sendrecv(s->comm, send_lo, sl, recv_lo, rl, send_hi, sh, recv_hi, rh, s->stream))) break;
+        if ((rc = crm_sim_ghosts_refresh(s, rank > 0 ? recv_lo : nullptr, rank + 1 < world ? recv_hi : nullptr))) break;
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
+        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, s->stream);
+        if (s->timers && k == 0) {
+            CK(cudaEventRecord(s->ev1, s->stream));
+            CK(cudaEventRecord(s->ev2, s->stream));
+        }
+        launch_integrate(s->nv, s->d, s->stream);
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
+        k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, s->skin, 0u, s->flags_dev);
+        if ((rc = crm_comm_allgather(s->comm, s->flags_dev, s->flags_dev + 4, 16, s->stream))) break;
+        k_latch_from_flags<<<1, 32, 0, s->stream>>>(s->flags_dev + 4, world, s->latch_buf, (uint32_t)s->d.iteration);
+        s->launches += 4;
+    }
+    s->d.latch = nullptr;
+    s->bounds_fresh = false;
+    if (rc) return rc;  // (a transport failure: nothing sensible can follow)
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaMemcpyAsync(h_latch, s->latch_buf, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaMemcpyAsync(s->flags_host, s->flags_dev + 4, sizeof(uint32_t) * 4 * world, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaEventRecord(s->ev_status, s->stream));
+    CK(cudaEventSynchronize(s->ev_status));
+    const uint32_t stop = *h_latch;
+    const uint32_t n_done = stop ? (uint32_t)(stop - (uint32_t)it0) : B;
+    if (n_done == 0 || n_done > B) return fail(CRM_ERR_CUDA, "sharded steps: latch out of range (%u of %u)", n_done, B);
+    s->iteration = it0 + n_done;
+    s->d.iteration = s->iteration;
+    s->rod_steps += (uint64_t)s->n * n_done;
+    s->n_eval_steps += n_done;
+    s->evals_since_build += n_done;
+    s->steps_since_build += n_done;
+    s->n_batches += 1;
+    s->batch_len = stop ? std::max<uint32_t>(1u, n_done) : std::min<uint32_t>(2u * B, 64u);
+    if (s->timers) {
+        float ms = 0.0f;
+        CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        s->force_ms += ms;
+        s->force_launches += 1;
+        CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+        s->integrate_ms += ms;
+        s->integrate_launches += 1;
+    }
+    *done = n_done;
+    memcpy(flags_out, s->flags_host, sizeof(uint32_t) * 4 * world);
+    return step_conclude(s);
 }
 
 int crm_sim_step_timed(crm_sim* s, uint32_t n_steps, double* ms_out) {

@@ -66,6 +66,15 @@ struct HostSnap {
     std::vector<uint32_t> sim_of;
 };
 
+// NCCL transport of the sharded step loop (crm_comm.cu)
+struct crm_comm;
+int crm_comm_rank(const crm_comm* c);
+int crm_comm_world(const crm_comm* c);
+int crm_comm_sendrecv(crm_comm* c, const void* send_lo, size_t n_send_lo, void* recv_lo, size_t n_recv_lo,
+                      const void* send_hi, size_t n_send_hi, void* recv_hi, size_t n_recv_hi, cudaStream_t st);
+int crm_comm_allgather(crm_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+void crm_comm_free(crm_comm* c);
+
 struct crm_sim {
     crm_config cfg{};
     int device = 0;
@@ -129,6 +138,9 @@ struct crm_sim {
     uint32_t ghost_n[2] = {0, 0};  // ghosts installed from the lower / upper message (crm_sim_ghosts_refresh)
     float slab_lo = -INFINITY, slab_hi = INFINITY;
     uint32_t pending_div = 0;  // divisions of the last step awaiting crm_sim_apply_divisions
+    crm_comm* comm = nullptr;        // communicator of all slabs (crm_sim_comm_init)
+    uint32_t* flags_dev = nullptr;   // [4] this slab's flags of a step, [4 * world] the gathered ones behind them
+    uint32_t* flags_host = nullptr;  // pinned [4 * world]
     void* select_tmp = nullptr;  // cub temp storage
     size_t select_tmp_bytes = 0;
     uint32_t* select_out = nullptr;  // [select_cap] selected slots

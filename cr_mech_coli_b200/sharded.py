@@ -30,6 +30,10 @@ HEADER_BYTES = 64  # message header: int32 n_records, float32 max_extent
 # steps between two rebuilds run stream-ordered (no host wait between pack, transport, ghosts, step and
 # the flag all_gather); CRM_B200_SYNC_HALO=1 selects the synchronous protocol for comparison
 STREAM_ORDERED = os.environ.get("CRM_B200_SYNC_HALO", "0") != "1"
+# the step loop between two rebuilds runs in the C++ host with NCCL called directly (crm_sim_steps_sharded: whole
+# batches of steps incl. their exchanges, one status read-back per batch); CRM_B200_PY_COORD=1 keeps the
+# per-step Python coordinator (torch.distributed transport) for comparison
+CPP_COORDINATOR = os.environ.get("CRM_B200_PY_COORD", "0") != "1"
 
 
 # --------------------------------------------------------------------------------------------
@@ -265,6 +269,28 @@ class Shard:
     def step_end(self):
         self.lib.check(self.lib.fn("sim_step_end")(self.sim.h))
         return self._step_result()
+
+    def comm_init(self, uid: bytes, rank: int, world: int):
+        """Joins the NCCL communicator of all slabs (collective)."""
+        buf = (C.c_char * 128).from_buffer_copy(uid)
+        self.lib.check(self.lib.fn("sim_comm_init")(self.sim.h, buf, rank, world))
+
+    def steps_sharded(self, n_max: int, world: int):
+        """Up to ``n_max`` list steps incl. their halo exchanges, enqueued by the C++ host (collective).  Returns
+        (steps done, flags[world, 4], SimulationError of this slab or None)."""
+        done = C.c_uint32(0)
+        flags = np.zeros(4 * world, dtype=np.uint32)
+        send, recv = self._msg_ptrs(self.send), self._msg_ptrs(self.recv)
+        rc = self.lib.fn("sim_steps_sharded")(self.sim.h, int(n_max), send[0], send[1], recv[0], recv[1], C.byref(done),
+                                              flags.ctypes.data_as(C.c_void_p))
+        err = None
+        if rc < 0:
+            kind = _capi.STATUS_NAMES.get(rc, f"error {rc}")
+            err = _capi.SimulationError(f"{kind}: {self.lib.last_error()}")
+            if rc not in (_capi.ERR_BOUNDARY, _capi.ERR_NUMERIC, _capi.ERR_DIVISION):
+                raise err  # not a model error: the transport or the device failed
+        self.n_self = 0
+        return int(done.value), flags.reshape(world, 4).astype(np.float64), err
 
     def install_ghosts(self):
         """Ghosts of this step from the received messages + the own leavers.  Returns (counts,
@@ -568,6 +594,18 @@ class DistributedShard:
         self.emax_global = 0.0
         self._flags_all = self._flags_host = None
         self._halo_ahead = False
+        self.cpp = False
+        if CPP_COORDINATOR and self.tr.device.type == "cuda" and self.world > 1:
+            # communicator of the C++ step loop: the unique id travels over the process group
+            uid = [None]
+            if self.rank == 0:
+                b = (C.c_char * 128)()
+                lib.check(lib.fn("comm_unique_id")(b))
+                uid[0] = bytes(b.raw)
+            self.tr.dist.broadcast_object_list(uid, src=self.tr.dist.get_global_rank(group, 0) if group is not None else 0,
+                                               group=group)
+            self.shard.comm_init(uid[0], self.rank, self.world)
+            self.cpp = True
 
     def close(self):
         self.shard.close()
@@ -675,8 +713,21 @@ class DistributedShard:
                 gc.enable()
 
     def _steps(self, n_steps: int):
-        for _ in range(n_steps):
-            if STREAM_ORDERED and self.use_lists and not self.rebuild_next:
+        remaining = int(n_steps)
+        while remaining > 0:
+            done = 1
+            if self.cpp and STREAM_ORDERED and self.use_lists and not self.rebuild_next:
+                # between two rebuilds: whole batches of steps from the C++ host, one host wait per batch
+                with self.tr.torch.cuda.stream(self.shard.stream):
+                    done, st, own = self.shard.steps_sharded(remaining, self.world)
+                self._halo_ahead = False
+                self.moved = False
+                if st[:, 2].max() > 0:
+                    self.iteration += done - 1
+                    self._raise_collective(st[:, 2], own)
+                self.shard._step_result()
+                self.iteration += done
+            elif STREAM_ORDERED and self.use_lists and not self.rebuild_next:
                 st = self._frozen_step()
                 self.iteration += 1
             else:
@@ -695,6 +746,7 @@ class DistributedShard:
                 if st[:, 2].max() > 0:
                     self._raise_collective(st[:, 2], own)
                 self.iteration += 1
+            remaining -= done
             self.rebuild_next = bool(st[:, 1].max() > 0) or not self.use_lists
             if st[:, 0].sum() > 0:
                 gs, vx = self.shard.pending_divisions()

@@ -358,6 +358,22 @@ int crm_sim_snapshot_global_slots(const crm_sim* sim, uint32_t k, uint64_t* out)
  * figure implies at 128 lanes/SM/clk. */
 int crm_microbench(int device, double* fp32_tflops, double* mufu_tops, double* sm_mhz_est);
 
+/* ---- sharded step loop in the C++ host (NCCL over NVLink) ------------------------------------------------
+ * The reference's sub-domain threads exchange boundary agents without a global barrier per aspect (reference
+ * src/simulation.rs:251-256,283-292).  Here one process per GPU joins a communicator; between two collective
+ * rebuilds crm_sim_steps_sharded enqueues whole batches of steps with their halo send/recv and the all-gather of
+ * the per-step flags on the sim's stream and reads ONE status block per batch (csrc/crm_sim.cu, crm_comm.cu).
+ * NCCL is bound at run time (dlopen libnccl.so.2); without it these calls fail, nothing else is affected. */
+/* 128-byte unique id made by one rank; the caller hands it to all ranks (any side channel). */
+int crm_comm_unique_id(void* out128);
+/* Collective: joins the slab `sim` (crm_sim_set_slab) to the communicator; rank r owns slab r. */
+int crm_sim_comm_init(crm_sim* sim, const void* id128, int rank, int world);
+/* Collective: up to n_max list steps incl. their exchanges; the four device buffers are those of
+ * crm_sim_halo_pack_msgs / crm_sim_set_ghosts_msgs.  *done = steps advanced, flags_out[4 * world] = {divisions,
+ * rebuild wish, -error code, 0} per slab for the last of them. */
+int crm_sim_steps_sharded(crm_sim* sim, uint32_t n_max, void* send_lo, void* send_hi, void* recv_lo, void* recv_hi,
+                          uint32_t* done, uint32_t* flags_out);
+
 /* ---- 2-D mask path: the step after the mechanics in the crm_divide objective ------------
  * Host buffers in and out; kernels in csrc/crm_raster.cu.  No graphics API is involved. */
 /* Replaces `calculate_polygon_hull` (reference src/fitting.rs:514-620): the capsule-chain outline of each of

@@ -103,9 +103,10 @@ def test_render_mask_2d_and_parents_diff_through_the_mirror(product_lib):
     parent_of = np.array([index[container.parent_map[c]] if container.parent_map[c] is not None else -1 for c in cells],
                          np.int32)
     assert np.array_equal(d, raster.parents_diff(m0, m1, table, parent_of, 0.5))
-    with pytest.raises(KeyError):
+    with pytest.raises(KeyError):  # an unknown colour facing a cell (facing background it is just "different")
         bad = m1.copy()
-        bad[0, 0] = counter_to_color(77)
+        y, x = np.argwhere(m0.any(axis=2))[0]
+        bad[y, x] = counter_to_color(77)
         fitting.parents_diff_mask(m0, bad, container.color_to_cell, container.parent_map)
     with pytest.raises(ValueError):
         fitting.parents_diff_mask(m0, m1[:10], container.color_to_cell, container.parent_map)
