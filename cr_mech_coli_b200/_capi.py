@@ -209,7 +209,9 @@ class Library:
             "overlap": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, P(C.c_float)]),
             "parents_diff_mask": (C.c_int, [vp, vp, u64, vp, u32, vp, u32, C.c_float, vp, P(C.c_int64)]),
             "comm_unique_id": (C.c_int, [vp]),
-            "sim_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+            "comm_create": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, P(vp)]),
+            "comm_destroy": (None, [vp]),
+            "sim_set_comm": (C.c_int, [vp, vp]),
             "sim_steps_sharded": (C.c_int, [vp, u32, vp, vp, vp, vp, P(u32), vp]),
             "host_alloc": (vp, [C.c_size_t]),
             "host_free": (None, [vp]),

@@ -123,16 +123,13 @@ int crm_comm_unique_id(void* out128) {
     return 0;
 }
 
-// Joins the sim (one slab, crm_sim_set_slab) to the communicator of all slabs; rank r owns slab r.  Collective.
-int crm_sim_comm_init(crm_sim* s, const void* id128, int rank, int world) {
-    if (!s || !id128 || rank < 0 || rank >= world) return crm_fail(CRM_ERR_INVALID, "bad communicator arguments");
+// Communicator of all slabs on `device`; rank r owns slab r.  Collective.  A communicator outlives the sims that
+// use it (its connections are set up lazily by the first transfers, hundreds of milliseconds: made once per job).
+int crm_comm_create(const void* id128, int rank, int world, int device, crm_comm** out) {
+    if (!id128 || !out || rank < 0 || rank >= world) return crm_fail(CRM_ERR_INVALID, "bad communicator arguments");
     Api* a = api();
     if (!a->handle) return crm_fail(CRM_ERR_CUDA, "NCCL unavailable: %s", a->error.c_str());
-    CK(cudaSetDevice(s->device));
-    if (s->comm) {
-        crm_comm_free(s->comm);
-        s->comm = nullptr;
-    }
+    CK(cudaSetDevice(device));
     ncclUniqueId id;
     memcpy(&id, id128, sizeof(id));
     crm_comm* c = new crm_comm();
@@ -143,6 +140,14 @@ int crm_sim_comm_init(crm_sim* s, const void* id128, int rank, int world) {
         delete c;
         return crm_fail(CRM_ERR_CUDA, "ncclCommInitRank failed: %s", a->GetErrorString(r));
     }
+    *out = c;
+    return 0;
+}
+void crm_comm_destroy(crm_comm* c) { crm_comm_free(c); }
+
+// The slab `s` (crm_sim_set_slab) steps with this communicator (borrowed, not owned).
+int crm_sim_set_comm(crm_sim* s, crm_comm* c) {
+    if (!s) return crm_fail(CRM_ERR_INVALID, "null sim");
     s->comm = c;
     return 0;
 }

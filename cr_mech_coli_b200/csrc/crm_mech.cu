@@ -233,6 +233,8 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
     // a step of a batch behind the one that latched (blocks of the latching step itself read their own
     // iteration or 0 and go on)
     if (stop != 0u && stop < (unsigned)d.iteration) return;
+    // (a search step whose cell grid turned out too fine for the rods: the host repeats it, see Dev::emax_limit_bits)
+    if (d.skip && *d.skip) return;
 
     // neighbours
     float Pn[3], Pp[3];

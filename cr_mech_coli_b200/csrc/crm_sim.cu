@@ -35,18 +35,14 @@ static void parallel_for(size_t n, F f) {
     for (auto& t : th) t.join();
 }
 
-// new zeroed array holding the first `old_count` elements of the old one; the old block is freed by the
-// caller after ONE synchronisation for all arrays (`retired`)
-template <class T>
-static int regrow(T*& ptr, size_t old_count, size_t new_count, cudaStream_t st, std::vector<void*>& retired) {
-    T* np_ = nullptr;
-    CK(cudaMalloc(&np_, sizeof(T) * new_count));
-    CK(cudaMemsetAsync(np_, 0, sizeof(T) * new_count, st));
-    if (ptr && old_count) CK(cudaMemcpyAsync(np_, ptr, sizeof(T) * old_count, cudaMemcpyDeviceToDevice, st));
-    if (ptr) retired.push_back(ptr);
-    ptr = np_;
-    return 0;
-}
+// All per-rod arrays live in ONE device allocation (an arena): a colony of 1e6 rods needs ~45 arrays, and 45
+// cudaMalloc calls cost more than moving the colony across the bus (they dominated the upload of the end-to-end
+// path and varied 4x between hosts).  Growth allocates a new arena, copies what must survive, frees the old one.
+struct ArenaItem {
+    void** pptr;
+    size_t elem, old_count, new_count;
+    int fill;  // byte the fresh part is set to (0 or 0xff)
+};
 
 // grow every per-rod array to `need` slots, preserving the first s->n
 int crm_reserve(crm_sim* s, uint32_t need) {
@@ -56,9 +52,8 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     while (cap < need) cap *= 2;
     const size_t st_ = (size_t)3 * s->lp;
     const size_t on = s->n, oc = (size_t)s->n * st_;
-    int rc;
-    std::vector<void*> retired;
-#define G(p, cnt_old, cnt_new) if ((rc = regrow(p, cnt_old, cnt_new, s->stream, retired))) return rc
+    std::vector<ArenaItem> items;
+#define G(p, cnt_old, cnt_new) items.push_back(ArenaItem{reinterpret_cast<void**>(&(p)), sizeof(*(p)), (size_t)(cnt_old), (size_t)(cnt_new), 0})
     G(s->d.pos, oc, cap * st_);
     G(s->d.vel, oc, cap * st_);
     G(s->d.force, oc, cap * st_);
@@ -88,13 +83,9 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.dextra, 0, (size_t)cap * PATCH_EXTRA);
     G(s->d.dmark, 0, (size_t)cap);
     G(s->d.dsib, 0, (size_t)cap);
+    items.back().fill = 0xff;
     G(s->d.dirty_list, 0, (size_t)cap);
-    CK(cudaMemsetAsync(s->d.dsib, 0xff, sizeof(uint32_t) * cap, s->stream));
-    if (!s->d.dirty_n) CK(cudaMalloc(&s->d.dirty_n, sizeof(uint32_t)));
-    CK(cudaMemsetAsync(s->d.dirty_n, 0, sizeof(uint32_t), s->stream));
-    s->n_dirty = 0;
-    s->need_rebuild = true;  // the structure does not survive a reallocation
-    s->have_lists = false;
+    G(s->d.dirty_n, 0, (size_t)1);
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
     G(s->d.sorted, 0, (size_t)cap);
@@ -104,8 +95,34 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->stage, 0, (size_t)cap * s->nv * 3);
     G(s->stage2, 0, (size_t)cap * s->nv * 3);
 #undef G
-    CK(cudaStreamSynchronize(s->stream));
-    for (void* q : retired) CK(cudaFree(q));
+    size_t total = 0;
+    std::vector<size_t> off(items.size());
+    for (size_t i = 0; i < items.size(); ++i) {
+        off[i] = total;
+        total += (items[i].elem * items[i].new_count + 255) / 256 * 256;
+    }
+    char* arena = nullptr;
+    if (cudaMalloc(&arena, total) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(CRM_ERR_NOMEM, "out of device memory: %zu bytes for %u rod slots", total, cap);
+    }
+    // fresh parts are zeroed (only what is not overwritten by the copy), surviving parts copied
+    for (size_t i = 0; i < items.size(); ++i) {
+        const ArenaItem& it = items[i];
+        char* dst = arena + off[i];
+        const size_t keep = (*it.pptr && it.old_count) ? it.elem * it.old_count : 0;
+        if (keep) CK(cudaMemcpyAsync(dst, *it.pptr, keep, cudaMemcpyDeviceToDevice, s->stream));
+        CK(cudaMemsetAsync(dst + keep, it.fill, it.elem * it.new_count - keep, s->stream));
+        *it.pptr = dst;
+    }
+    if (s->arena) {  // the copies out of the old arena must have finished
+        CK(cudaStreamSynchronize(s->stream));
+        CK(cudaFree(s->arena));
+    }
+    s->arena = arena;
+    s->n_dirty = 0;
+    s->need_rebuild = true;  // the structure does not survive a reallocation
+    s->have_lists = false;
     s->d.divcap = cap;
     s->d.tile = s->sim_of.empty() ? nullptr : s->tile_buf;
     s->d.rkey = s->rkey_on ? s->rkey_buf : nullptr;
@@ -142,8 +159,9 @@ static int reserve_cells(crm_sim* s, uint32_t ncells) {
 static bool persistent(const crm_sim* s) { return s->skin > 0.0f; }
 static float search_radius(const crm_sim* s) { return s->rsearch + (persistent(s) ? s->skin : 0.0f); }
 
-static int configure_grid(crm_sim* s) {
-    const float h = (2.0f * std::max(s->emax, s->n_ghost ? s->emax_ghost : 0.0f) + search_radius(s)) * 1.0005f + 1e-4f;
+static int configure_grid(crm_sim* s, float emax_own = -1.0f) {
+    if (emax_own < 0.0f) emax_own = s->emax;
+    const float h = (2.0f * std::max(emax_own, s->n_ghost ? s->emax_ghost : 0.0f) + search_radius(s)) * 1.0005f + 1e-4f;
     double ncx = std::floor((double)s->cfg.domain_size[0] / h), ncy = std::floor((double)s->cfg.domain_size[1] / h);
     if (!(ncx >= 1.0)) ncx = 1.0;
     if (!(ncy >= 1.0)) ncy = 1.0;
@@ -267,12 +285,71 @@ int crm_report_device_error(crm_sim* s) {
 // backend's update_cell_cycle_4 (mothers are renamed first, then the new cells, with the per-voxel
 // pre-incremented counter).  Unsharded runs derive the identifiers here; sharded runs get them from
 // the coordinator, which sees the divisions of all slabs (crm_sim_apply_divisions).
+// one block: the division list ordered by (global slot, slot) on the device (bitonic sort in shared memory).  The
+// atomic appends of k_integrate arrive in any order; the order fixes identifiers and daughter slots.
+constexpr uint32_t DIV_SORT_MAX = 2048;
+__global__ void __launch_bounds__(1024) k_div_sort(DivRecord* list, uint32_t n, const uint32_t* __restrict__ rkey) {
+    __shared__ unsigned long long key[DIV_SORT_MAX];
+    __shared__ uint32_t vox[DIV_SORT_MAX];
+    uint32_t m = 1;
+    while (m < n) m <<= 1;
+    for (uint32_t i = threadIdx.x; i < m; i += blockDim.x) {
+        if (i < n) {
+            const DivRecord r = list[i];
+            key[i] = ((unsigned long long)(rkey ? rkey[r.slot] : r.slot) << 32) | r.slot;
+            vox[i] = r.uvox;
+        } else {
+            key[i] = ~0ull;
+            vox[i] = 0;
+        }
+    }
+    __syncthreads();
+    for (uint32_t k = 2; k <= m; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t i = threadIdx.x; i < m; i += blockDim.x) {
+                const uint32_t l = i ^ j;
+                if (l > i) {
+                    const bool up = (i & k) == 0;
+                    if ((key[i] > key[l]) == up) {
+                        const unsigned long long t = key[i]; key[i] = key[l]; key[l] = t;
+                        const uint32_t v = vox[i]; vox[i] = vox[l]; vox[l] = v;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        list[i].slot = (uint32_t)(key[i] & 0xffffffffull);
+        list[i].uvox = vox[i];
+    }
+}
+
+// Divisions of this step.  The mothers are ordered by global slot (= slot when the run is not sharded) on the
+// device; the geometry kernel, the patch kernels and the read-back of the ordered list are enqueued together and
+// the host waits ONCE, then installs the identifiers of the backend's update_cell_cycle_4 (mothers are renamed
+// first, then the new cells, with the per-voxel pre-incremented counter).  Unsharded runs derive the
+// identifiers here; sharded runs get them from the coordinator, which sees the divisions of all slabs
+// (fetch_divisions -> crm_sim_pending_divisions -> crm_sim_apply_divisions).
+static int sort_divisions_on_device(crm_sim* s, uint32_t n_div) {
+    if (n_div > 1 && n_div <= DIV_SORT_MAX) {
+        k_div_sort<<<1, 1024, 0, s->stream>>>(s->d.divlist, n_div, s->d.rkey);
+        s->launches += 1;
+        return 1;
+    }
+    return n_div <= 1 ? 1 : 0;
+}
+
 static int fetch_divisions(crm_sim* s, uint32_t n_div) {
+    const int sorted = sort_divisions_on_device(s, n_div);
     s->h_div.resize(n_div);
     CK(cudaMemcpyAsync(s->h_div.data(), s->d.divlist, sizeof(DivRecord) * n_div, cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
-    std::sort(s->h_div.begin(), s->h_div.end(),
-              [s](const DivRecord& a, const DivRecord& b) { return s->gslot[a.slot] < s->gslot[b.slot]; });
+    if (!sorted) {  // (more divisions in one step than the one-block sort takes)
+        std::sort(s->h_div.begin(), s->h_div.end(), [s](const DivRecord& a, const DivRecord& b) {
+            return s->gslot[a.slot] != s->gslot[b.slot] ? s->gslot[a.slot] < s->gslot[b.slot] : a.slot < b.slot;
+        });
+        CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
+    }
     for (uint32_t r = 0; r < n_div; ++r) {
         const crm_rod_params& p = s->base[s->h_div[r].slot];
         if (!(p.radius > 0.0f))
@@ -281,27 +358,27 @@ static int fetch_divisions(crm_sim* s, uint32_t n_div) {
     return 0;
 }
 
-int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident* id_daughter,
-                           const uint64_t* gslot_daughter) {
-    const uint32_t n0 = s->n, n_div = (uint32_t)s->h_div.size();
-    int rc = crm_reserve(s, n0 + n_div);
-    if (rc) return rc;
-    CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
+// geometry + (optionally) the patch of the live neighbour structure for the ordered list on the device; status
+// zeroed in front, nothing waits
+static int divisions_enqueue(crm_sim* s, uint32_t n_div, uint32_t n0, bool patch, uint32_t* h_dirty) {
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     launch_divide(s->nv, s->d, n_div, n0, s->stream);
     s->launches += 1;
-    // Divisions were the only reason to search again and the structure is live: patch it (the rows of the
-    // daughters and of the mothers' neighbours are rebuilt from candidate lists at the start of the next step)
-    const bool patch = s->patch_divisions && s->have_lists && !s->need_rebuild && !s->sharded && s->skin > 0.0f;
-    s->patch_divisions = false;
-    uint32_t* const h_dirty = reinterpret_cast<uint32_t*>(s->h_status + 1) + 16;  // pinned scratch behind the status
     if (patch) {
         CK(cudaMemsetAsync(s->d.dirty_n, 0, sizeof(uint32_t), s->stream));
         s->launches += launch_patch(s->d, n_div, n0, s->lp, s->lp > 8 ? 8 : 16, s->stream);
         CK(cudaMemcpyAsync(h_dirty, s->d.dirty_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
     }
     CK(cudaGetLastError());
-    if ((rc = crm_read_status(s))) return rc;
+    return 0;
+}
+
+// host bookkeeping of the divisions in s->h_div (ordered), after the kernels' status has arrived
+static int divisions_bookkeep(crm_sim* s, uint32_t n0, bool patch, const uint32_t* h_dirty, const crm_ident* id_mother,
+                              const crm_ident* id_daughter, const uint64_t* gslot_daughter) {
+    const uint32_t n_div = (uint32_t)s->h_div.size();
+    int rc;
+    crm_note_list_flags(s);
     if ((rc = crm_report_device_error(s))) return rc;
     bool patched = false;
     if (patch) {
@@ -345,10 +422,21 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     return 0;
 }
 
-static int handle_divisions(crm_sim* s, uint32_t n_div) {
-    int rc = fetch_divisions(s, n_div);
+// sharded runs: the ordered list is already on both sides (fetch_divisions), the identifiers come from the coordinator
+int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident* id_daughter,
+                           const uint64_t* gslot_daughter) {
+    const uint32_t n0 = s->n, n_div = (uint32_t)s->h_div.size();
+    int rc = crm_reserve(s, n0 + n_div);
     if (rc) return rc;
-    const uint32_t n0 = s->n;
+    s->patch_divisions = false;  // (sharded runs search again after a division: it is a collective decision)
+    if ((rc = divisions_enqueue(s, n_div, n0, false, nullptr))) return rc;
+    if ((rc = crm_read_status(s))) return rc;
+    return divisions_bookkeep(s, n0, false, nullptr, id_mother, id_daughter, gslot_daughter);
+}
+
+// identifiers of an unsharded division step from the ordered list in s->h_div, then the bookkeeping
+static int divisions_ids_and_bookkeep(crm_sim* s, uint32_t n0, bool patch, const uint32_t* h_dirty) {
+    const uint32_t n_div = (uint32_t)s->h_div.size();
     const uint32_t nvox = s->cfg.n_voxels[0] * s->cfg.n_voxels[1];
     const bool batched = !s->sim_of.empty();
     // counters are per (sim, user voxel); mothers come ordered by slot, which inside a sim is the
@@ -367,7 +455,40 @@ static int handle_divisions(crm_sim* s, uint32_t n_div) {
         gs[r] = batched ? s->sim_rods[s->sim_of[s->h_div[r].slot]]++ : (uint64_t)n0 + r;
     }
     for (size_t kv = 0; kv < per_vox.size(); ++kv) s->vox_counter[kv] += 2ull * per_vox[kv];
-    return crm_apply_divisions(s, idm.data(), idd.data(), gs.data());
+    return divisions_bookkeep(s, n0, patch, h_dirty, idm.data(), idd.data(), gs.data());
+}
+
+static int handle_divisions(crm_sim* s, uint32_t n_div) {
+    const uint32_t n0 = s->n;
+    int rc;
+    // Divisions were the only reason to search again and the structure is live: patch it (the rows of the
+    // daughters and of the mothers' neighbours are rebuilt from candidate lists at the start of the next step)
+    const bool patch = s->patch_divisions && s->have_lists && !s->need_rebuild && !s->sharded && s->skin > 0.0f;
+    s->patch_divisions = false;
+    uint32_t* const h_dirty = reinterpret_cast<uint32_t*>(s->h_status + 1) + 16;  // pinned scratch behind the status
+    const bool grow = n0 + n_div > s->cap;
+    if (grow || n_div > DIV_SORT_MAX || n_div > s->h_div_pinned_cap) {
+        // the arrays move (the live structure does not survive that) or the list is too long for the one-block
+        // sort: order it through the host first
+        if ((rc = fetch_divisions(s, n_div))) return rc;
+        if ((rc = crm_reserve(s, n0 + n_div))) return rc;
+        const bool p2 = patch && !grow;
+        if ((rc = divisions_enqueue(s, n_div, n0, p2, h_dirty))) return rc;
+        if ((rc = crm_read_status(s))) return rc;
+        return divisions_ids_and_bookkeep(s, n0, p2, h_dirty);
+    }
+    // everything on the device, one wait: order the list, read it back (page-locked), divide, patch, status
+    sort_divisions_on_device(s, n_div);
+    CK(cudaMemcpyAsync(s->h_div_pinned, s->d.divlist, sizeof(DivRecord) * n_div, cudaMemcpyDeviceToHost, s->stream));
+    if ((rc = divisions_enqueue(s, n_div, n0, patch, h_dirty))) return rc;
+    if ((rc = crm_read_status(s))) return rc;
+    s->h_div.assign(s->h_div_pinned, s->h_div_pinned + n_div);
+    for (uint32_t r = 0; r < n_div; ++r) {
+        const crm_rod_params& p = s->base[s->h_div[r].slot];
+        if (!(p.radius > 0.0f))
+            return fail(CRM_ERR_DIVISION, "DivisionError: cannot divide rod slot %u (radius %g)", s->h_div[r].slot, p.radius);
+    }
+    return divisions_ids_and_bookkeep(s, n0, patch, h_dirty);
 }
 
 // Bounds of the search (bounding sphere, chord, cull thresholds, max extent) for the current
@@ -387,15 +508,39 @@ int crm_refresh_bounds(crm_sim* s) {
     return 0;
 }
 
-static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false) {
-    int rc = crm_refresh_bounds(s);
-    if (rc) return rc;
-    if ((rc = configure_grid(s))) return rc;
-    s->d.n = s->n + s->n_ghost;
-    s->d.n_own = s->n;
-    s->d.rsearch = search_radius(s);
-    s->d.skin = s->skin;
-    CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+__global__ void k_grid_check(const Status* st, uint32_t limit_bits, uint32_t* skip) { *skip = st->emax_bits > limit_bits ? 1u : 0u; }
+
+// `async_bounds` (search steps of crm_sim_step & co.): the bounds kernel is enqueued in front of the search without
+// waiting for its result; the grid is sized with head-room over the last known extent and the kernels of the step
+// return at once should a rod exceed it (Dev::emax_limit_bits; step_finish then repeats the step the slow way).
+static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false, bool async_bounds = false) {
+    int rc;
+    s->d.emax_limit_bits = 0u;
+    s->d.skip = nullptr;
+    s->async_search = false;
+    if (async_bounds && !s->bounds_fresh && !s->sharded && s->n > 0 && s->emax > 0.0f && std::isfinite(s->emax)) {
+        const float emax_cfg = s->emax * 1.05f + 0.05f;
+        if ((rc = configure_grid(s, emax_cfg))) return rc;
+        s->d.n = s->n + s->n_ghost;
+        s->d.n_own = s->n;
+        s->d.rsearch = search_radius(s);
+        s->d.skin = s->skin;
+        CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+        launch_bounds_kernel(s->nv, s->d, s->stream);  // status->emax_bits: read by the kernels below, and by the host after the step
+        s->d.emax_limit_bits = __builtin_bit_cast(uint32_t, emax_cfg);
+        k_grid_check<<<1, 1, 0, s->stream>>>(s->d.status, s->d.emax_limit_bits, s->latch_buf + 2);
+        s->launches += 2;
+        s->d.skip = s->latch_buf + 2;
+        s->async_search = true;
+    } else {
+        if ((rc = crm_refresh_bounds(s))) return rc;
+        if ((rc = configure_grid(s))) return rc;
+        s->d.n = s->n + s->n_ghost;
+        s->d.n_own = s->n;
+        s->d.rsearch = search_radius(s);
+        s->d.skin = s->skin;
+        CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    }
     s->launches += launch_binning(s->d, s->n_sims, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
     if (build) s->lists_slow = s->lists_morse = s->lists_mie = false;  // until this step's status says otherwise (read before any list step)
@@ -407,6 +552,9 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
 
 // force of a step between two rebuilds: no cell list, no search (k_force_eval)
 static int launch_force_from_lists(crm_sim* s) {
+    s->d.emax_limit_bits = 0u;
+    s->d.skip = nullptr;
+    s->async_search = false;
     s->d.n = s->n + s->n_ghost;  // the build order covers the ghosts as well
     s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
@@ -468,7 +616,7 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
         s->evals_since_build += 1;
     } else {
         const bool build = persistent(s) && s->holdoff == 0;
-        rc = launch_neighbour_and_force(s, false, build);
+        rc = launch_neighbour_and_force(s, false, build, s->async_bounds);
         if (build) {
             // lists that repeatedly are not used (a colony with divisions in every step): stop writing them
             // for a while, twice as long every time it happens again (8 .. 512 steps)
@@ -549,6 +697,28 @@ static int step_finish(crm_sim* s) {
     // the step's own work only: what a caller enqueued behind it on the stream (the sharded coordinator's
     // next halo exchange) keeps running while the host decides what the next step is
     CK(cudaEventSynchronize(s->ev_status));
+    if (s->async_search) {
+        s->async_search = false;
+        const uint32_t bits = s->h_status->emax_bits;
+        s->emax = __builtin_bit_cast(float, bits);  // the extent k_bounds measured in front of this step's search
+        if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite positions (iteration %llu)",
+                                                 (unsigned long long)s->iteration);
+        if (bits > s->d.emax_limit_bits) {
+            // a rod outgrew the head-room the grid was sized with: the force and integrate kernels of the step
+            // returned without touching anything.  Repeat it with the bounds read back first.
+            s->iteration -= 1;
+            s->rod_steps -= s->n;
+            s->n_grid_redos += 1;
+            s->need_rebuild = true;
+            s->have_lists = false;
+            s->bounds_fresh = true;  // (k_bounds ran on the current positions and s->emax is its result)
+            const bool keep = s->async_bounds;
+            s->async_bounds = false;
+            const int rc = step_enqueue(s, nullptr);
+            s->async_bounds = keep;
+            return rc ? rc : step_finish(s);
+        }
+    }
     if (s->timers) {
         float ms = 0.0f;
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
@@ -576,6 +746,9 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
     const uint32_t B = std::max<uint32_t>(1u, std::min<uint32_t>(n_max, s->batch_len));
     s->d.n = s->n + s->n_ghost;
     s->d.n_own = s->n;
+    s->d.emax_limit_bits = 0u;
+    s->d.skip = nullptr;
+    s->async_search = false;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     CK(cudaMemsetAsync(s->latch_buf, 0, sizeof(uint32_t), s->stream));
     s->d.latch = s->latch_buf;
@@ -774,6 +947,8 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CK(cudaMalloc(&s->d.status, sizeof(Status)));
     CK(cudaMemset(s->d.status, 0, sizeof(Status)));
+    s->h_div_pinned_cap = DIV_SORT_MAX;
+    CK(cudaMallocHost(&s->h_div_pinned, sizeof(DivRecord) * s->h_div_pinned_cap));
     CK(cudaMalloc(&s->latch_buf, 256));
     CK(cudaMemset(s->latch_buf, 0, 256));
     CK(cudaMallocHost(&s->h_status, sizeof(Status) + 128));  // + pinned scratch (message headers)
@@ -783,6 +958,7 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaEventCreate(&s->ev3));
     CK(cudaEventCreateWithFlags(&s->ev_status, cudaEventDisableTiming));
     if (const char* bt = getenv("CRM_B200_BATCH")) s->batching = bt[0] != '0';
+    if (const char* ab = getenv("CRM_B200_ASYNC_BOUNDS")) s->async_bounds = ab[0] != '0';
     s->d.lx = c->domain_size[0];
     s->d.ly = c->domain_size[1];
     s->d.lz = c->domain_height;
@@ -808,15 +984,15 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
 void crm_sim_destroy(crm_sim* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    void* ptrs[] = {s->d.pos, s->d.vel, s->d.force, s->d.dx1, s->d.dv1, s->d.dx2, s->d.dv2, s->d.nhist, s->d.pot,
-                    s->d.mech, s->d.grow, s->d.cyc, s->d.nn, s->d.bsphere, s->d.chord, s->d.vrec, s->d.plist, s->d.pqo, s->d.pqe, s->d.pqs, s->d.pnq, s->d.vbuild, s->d.gof, s->d.dcnt, s->d.dextra, s->d.dmark, s->d.dsib, s->d.dirty_list, s->d.dirty_n, s->d.cell_of, s->d.cell_rank,
-                    s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0], s->halo_sel[1], s->tile_buf, s->sim_fail, s->d.sorted, s->d.bs_sorted, s->d.chord_sorted, s->d.divlist, s->d.status, s->stage, s->stage2, s->rkey_buf, s->latch_buf};
+    // (the per-rod arrays are parts of the arena)
+    void* ptrs[] = {s->arena, s->d.cell_start, s->d.cell_count, s->select_tmp, s->select_out, s->select_count, s->halo_sel[0],
+                    s->halo_sel[1], s->sim_fail, s->d.status, s->latch_buf};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (s->h_status) cudaFreeHost(s->h_status);
     if (s->flags_host) cudaFreeHost(s->flags_host);
+    if (s->h_div_pinned) cudaFreeHost(s->h_div_pinned);
     if (s->flags_dev) cudaFree(s->flags_dev);
-    if (s->comm) crm_comm_free(s->comm);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev2) cudaEventDestroy(s->ev2);
@@ -1187,7 +1363,7 @@ int crm_sim_step_end(crm_sim* s) {
 int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_hi, void* recv_lo, void* recv_hi,
                           uint32_t* done, uint32_t* flags_out) {
     if (!s || !done || !flags_out) return fail(CRM_ERR_INVALID, "null argument");
-    if (!s->comm) return fail(CRM_ERR_INVALID, "no communicator (crm_sim_comm_init)");
+    if (!s->comm) return fail(CRM_ERR_INVALID, "no communicator (crm_sim_set_comm)");
     if (!s->sharded || s->pending_div || s->step_open) return fail(CRM_ERR_INVALID, "not a slab ready to step");
     if (!persistent(s) || !s->have_lists || s->want_rebuild || s->n_dirty)
         return fail(CRM_ERR_INVALID, "no live neighbour structure: a collective rebuild step comes first");

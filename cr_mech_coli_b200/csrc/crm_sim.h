@@ -84,6 +84,7 @@ struct crm_sim {
     uint32_t n_ghost = 0;     // ghost rods in slots [n, n + n_ghost)
     uint32_t ncells_cap = 0;
     crm::Dev d{};
+    char* arena = nullptr;   // the one device allocation all per-rod arrays are parts of (crm_reserve)
     float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
     float* stage2 = nullptr; // second one: positions and velocities cross the bus back to back
     crm::Status* h_status = nullptr;  // pinned
@@ -127,6 +128,8 @@ struct crm_sim {
     std::vector<uint32_t> sim_rods0;     // batched sims: rods at set_agents (a sim that divided has more now)
     int* sim_fail = nullptr;             // device [n_sims], Dev::sim_fail points here while isolation is on
     std::vector<crm::DivRecord> h_div;
+    crm::DivRecord* h_div_pinned = nullptr;  // page-locked landing zone of the device-ordered division list
+    uint32_t h_div_pinned_cap = 0;
     uint64_t iteration = 0, rod_steps = 0, launches = 0;
     std::vector<uint64_t> save_iter;
     uint64_t max_iter = 0;
@@ -153,6 +156,9 @@ struct crm_sim {
     double integrate_ms = 0.0;
     uint64_t integrate_launches = 0;
     // batches of list steps (crm_sim.cu step_batch)
+    bool async_bounds = true;   // search steps do not wait for the bounds kernel (CRM_B200_ASYNC_BOUNDS=0: they do)
+    bool async_search = false;  // the step in flight is such a search step
+    uint64_t n_grid_redos = 0;  // search steps repeated because a rod outgrew the grid's head-room
     uint32_t* latch_buf = nullptr;  // device word (own cache line) the latching step writes its iteration to
     bool batching = true;      // CRM_B200_BATCH=0 / crm_sim_set_batching: one host round trip per step
     uint32_t batch_len = 4;    // steps of the next batch: doubles after a full batch (<= 64), shrinks to what a latched one served

@@ -270,10 +270,9 @@ class Shard:
         self.lib.check(self.lib.fn("sim_step_end")(self.sim.h))
         return self._step_result()
 
-    def comm_init(self, uid: bytes, rank: int, world: int):
-        """Joins the NCCL communicator of all slabs (collective)."""
-        buf = (C.c_char * 128).from_buffer_copy(uid)
-        self.lib.check(self.lib.fn("sim_comm_init")(self.sim.h, buf, rank, world))
+    def set_comm(self, comm):
+        """Steps with the (job-wide) NCCL communicator of all slabs."""
+        self.lib.check(self.lib.fn("sim_set_comm")(self.sim.h, comm))
 
     def steps_sharded(self, n_max: int, world: int):
         """Up to ``n_max`` list steps incl. their halo exchanges, enqueued by the C++ host (collective).  Returns
@@ -576,6 +575,27 @@ class Transport:
         return [r.cpu().numpy() for r in recv]
 
 
+_COMMS: dict = {}
+
+
+def _job_comm(lib, tr: "Transport", device: int, group):
+    """The NCCL communicator of the C++ step loop for this process group, created once per job (NCCL connects
+    lazily on the first transfers: hundreds of milliseconds).  The unique id travels over the process group."""
+    key = (id(group), int(device), tr.world)
+    if key not in _COMMS:
+        uid = [None]
+        if tr.rank == 0:
+            b = (C.c_char * 128)()
+            lib.check(lib.fn("comm_unique_id")(b))
+            uid[0] = bytes(b.raw)
+        tr.dist.broadcast_object_list(uid, src=tr.dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        comm = C.c_void_p()
+        buf = (C.c_char * 128).from_buffer_copy(uid[0])
+        lib.check(lib.fn("comm_create")(buf, tr.rank, tr.world, int(device), C.byref(comm)))
+        _COMMS[key] = comm
+    return _COMMS[key]
+
+
 class DistributedShard:
     """One slab per process; transport = ``torch.distributed`` (NCCL on GPUs).  Every rank calls
     the same methods in the same order."""
@@ -596,15 +616,7 @@ class DistributedShard:
         self._halo_ahead = False
         self.cpp = False
         if CPP_COORDINATOR and self.tr.device.type == "cuda" and self.world > 1:
-            # communicator of the C++ step loop: the unique id travels over the process group
-            uid = [None]
-            if self.rank == 0:
-                b = (C.c_char * 128)()
-                lib.check(lib.fn("comm_unique_id")(b))
-                uid[0] = bytes(b.raw)
-            self.tr.dist.broadcast_object_list(uid, src=self.tr.dist.get_global_rank(group, 0) if group is not None else 0,
-                                               group=group)
-            self.shard.comm_init(uid[0], self.rank, self.world)
+            self.shard.set_comm(_job_comm(lib, self.tr, device, group))
             self.cpp = True
 
     def close(self):

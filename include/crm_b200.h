@@ -366,8 +366,12 @@ int crm_microbench(int device, double* fp32_tflops, double* mufu_tops, double* s
  * NCCL is bound at run time (dlopen libnccl.so.2); without it these calls fail, nothing else is affected. */
 /* 128-byte unique id made by one rank; the caller hands it to all ranks (any side channel). */
 int crm_comm_unique_id(void* out128);
-/* Collective: joins the slab `sim` (crm_sim_set_slab) to the communicator; rank r owns slab r. */
-int crm_sim_comm_init(crm_sim* sim, const void* id128, int rank, int world);
+/* Collective: the communicator of all slabs (rank r owns slab r) on CUDA device `device`.  It outlives the sims
+ * that borrow it through crm_sim_set_comm (NCCL sets its connections up lazily, once per job). */
+typedef struct crm_comm crm_comm;
+int crm_comm_create(const void* id128, int rank, int world, int device, crm_comm** out);
+void crm_comm_destroy(crm_comm* comm);
+int crm_sim_set_comm(crm_sim* sim, crm_comm* comm);
 /* Collective: up to n_max list steps incl. their exchanges; the four device buffers are those of
  * crm_sim_halo_pack_msgs / crm_sim_set_ghosts_msgs.  *done = steps advanced, flags_out[4 * world] = {divisions,
  * rebuild wish, -error code, 0} per slab for the last of them. */

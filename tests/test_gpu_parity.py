@@ -43,7 +43,7 @@ def _abs_sum(o):
 
 def _assert_forces(g, o):
     """Both readings of the tolerance: colony-wide (largest force of the colony as the scale) and per vertex,
-    |Fg - Fo| <= 1e-5 |Fo| + 2e-6 x (summed |pair contributions| of that vertex)."""
+    |Fg - Fo| <= 1e-5 (|Fo| + summed |pair contributions| of that vertex)."""
     fg, ng = g.compute_forces()
     fo, no = o.compute_forces()
     assert np.isfinite(fg).all()
