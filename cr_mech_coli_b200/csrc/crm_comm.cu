@@ -68,6 +68,7 @@ Api* api() {
 struct crm_comm {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
+    bool fused = true;  // halo send/recv and the flag all-gather in one NCCL group (CRM_B200_NCCL_FUSED=0: two launches)
 };
 
 #define NK(call)                                                                                         \
@@ -95,6 +96,28 @@ int crm_comm_sendrecv(crm_comm* c, const void* send_lo, size_t n_send_lo, void* 
     }
     NK(a->GroupEnd());
     return 0;
+}
+
+int crm_comm_exchange(crm_comm* c, const void* send_lo, size_t n_send_lo, void* recv_lo, size_t n_recv_lo, const void* send_hi,
+                      size_t n_send_hi, void* recv_hi, size_t n_recv_hi, const void* flags, void* flags_all,
+                      size_t flag_bytes, cudaStream_t st) {
+    Api* a = api();
+    if (c->fused) {
+        NK(a->GroupStart());
+        if (c->rank > 0) {
+            if (n_send_lo) NK(a->Send(send_lo, n_send_lo, ncclUint8, c->rank - 1, c->comm, st));
+            if (n_recv_lo) NK(a->Recv(recv_lo, n_recv_lo, ncclUint8, c->rank - 1, c->comm, st));
+        }
+        if (c->rank + 1 < c->world) {
+            if (n_send_hi) NK(a->Send(send_hi, n_send_hi, ncclUint8, c->rank + 1, c->comm, st));
+            if (n_recv_hi) NK(a->Recv(recv_hi, n_recv_hi, ncclUint8, c->rank + 1, c->comm, st));
+        }
+        NK(a->AllGather(flags, flags_all, flag_bytes, ncclUint8, c->comm, st));
+        NK(a->GroupEnd());
+        return 0;
+    }
+    int rc = crm_comm_sendrecv(c, send_lo, n_send_lo, recv_lo, n_recv_lo, send_hi, n_send_hi, recv_hi, n_recv_hi, st);
+    return rc ? rc : crm_comm_allgather(c, flags, flags_all, flag_bytes, st);
 }
 
 int crm_comm_allgather(crm_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {
@@ -135,6 +158,7 @@ int crm_comm_create(const void* id128, int rank, int world, int device, crm_comm
     crm_comm* c = new crm_comm();
     c->rank = rank;
     c->world = world;
+    if (const char* f = getenv("CRM_B200_NCCL_FUSED")) c->fused = f[0] != '0';
     ncclResult_t r = a->CommInitRank(&c->comm, world, id, rank);
     if (r != ncclSuccess) {
         delete c;

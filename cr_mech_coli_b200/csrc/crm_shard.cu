@@ -67,6 +67,67 @@ __global__ void k_ghost_scatter(Dev d, const float4* __restrict__ in, uint32_t n
     else reinterpret_cast<float4*>(d.pot + a)[q - lp - 3] = v;
 }
 
+// ---- one launch per direction of a sharded step between rebuilds (crm_sim_steps_sharded) ---------------------
+// pack: both halo messages (headers + records of the frozen selections, [count | slots] lists) and this slab's
+// flags {divisions, rebuild wish, -error, 0} of the step that has just been integrated
+__global__ void k_halo_pack_all(Dev d, const uint32_t* __restrict__ sel_lo, uint32_t n_lo, const uint32_t* __restrict__ sel_hi,
+                                uint32_t n_hi, int lp, uint32_t* msg_lo, uint32_t* msg_hi, float emax, float skin,
+                                uint32_t* flags) {
+    const int rq = lp + 5;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) {
+        if (msg_lo) { msg_lo[0] = sel_lo[0]; msg_lo[1] = __float_as_uint(emax); msg_lo[2] = 0u; }
+        if (msg_hi) { msg_hi[0] = sel_hi[0]; msg_hi[1] = __float_as_uint(emax); msg_hi[2] = 0u; }
+        const Status* st = d.status;  // (the same conditions step_conclude evaluates on the host)
+        const float disp = sqrtf(__uint_as_float(st->disp2_bits));
+        uint32_t want = (st->n_div > 0) | (st->n_leave > 0) | (st->err_code != 0);
+        if (skin > 0.0f) want |= (st->plist_overflow != 0) | !(disp < 0.4999f * skin);
+        flags[0] = st->n_div;
+        flags[1] = want ? 1u : 0u;
+        flags[2] = (uint32_t)(-st->err_code);
+        flags[3] = 0u;
+    }
+    const uint32_t i = t / rq;
+    const int q = t % rq;
+    if (i >= n_lo + n_hi) return;
+    const bool lo = i < n_lo;
+    const uint32_t k = lo ? i : i - n_lo;
+    const uint32_t a = (lo ? sel_lo : sel_hi)[1 + k];
+    float4 v;
+    if (q < lp) v = d.vrec[(size_t)a * lp + q];
+    else if (q == lp) v = d.bsphere[a];
+    else if (q == lp + 1) v = d.chord[2 * a];
+    else if (q == lp + 2) v = d.chord[2 * a + 1];
+    else v = reinterpret_cast<const float4*>(d.pot + a)[q - lp - 3];
+    reinterpret_cast<float4*>((lo ? msg_lo : msg_hi) + 16)[(size_t)k * rq + q] = v;
+}
+
+// unpack: both received messages scattered to the ghost slots of the last rebuild step, and the gathered flags of
+// the PREVIOUS step turned into the batch's latch (first step in which any slab wants the host)
+__global__ void k_ghost_unpack_all(Dev d, const uint32_t* __restrict__ msg_lo, uint32_t n_lo, const uint32_t* __restrict__ msg_hi,
+                                   uint32_t n_hi, uint32_t first, int lp, const uint32_t* __restrict__ flags_all, int world,
+                                   uint32_t* latch, uint32_t iteration_prev) {
+    const int rq = lp + 5;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) {
+        uint32_t any = 0u;
+        for (int r = 0; r < world; ++r) any |= flags_all[4 * r] | flags_all[4 * r + 1] | flags_all[4 * r + 2];
+        if (any && *latch == 0u) *latch = iteration_prev;
+    }
+    const uint32_t i = t / rq;
+    const int q = t % rq;
+    if (i >= n_lo + n_hi) return;
+    const bool lo = i < n_lo;
+    const uint32_t k = lo ? i : i - n_lo;
+    const uint32_t a = first + i;  // lower neighbour's ghosts first, then the upper one's
+    const float4 v = reinterpret_cast<const float4*>((lo ? msg_lo : msg_hi) + 16)[(size_t)k * rq + q];
+    if (q < lp) d.vrec[(size_t)a * lp + q] = v;
+    else if (q == lp) d.bsphere[a] = v;
+    else if (q == lp + 1) d.chord[2 * a] = v;
+    else if (q == lp + 2) d.chord[2 * a + 1] = v;
+    else reinterpret_cast<float4*>(d.pot + a)[q - lp - 3] = v;
+}
+
 // full device state of a rod as 32-bit words: six [3][LP] matrices, then pot, mech, grow, cyc, nn, nhist
 __host__ __device__ inline int state_words(int lp) { return 18 * lp + 8 + 4 + 4 + 12 + 2; }
 
@@ -174,6 +235,29 @@ int select_band(crm_sim* s, float lo, float hi, uint32_t* n) {
 }
 
 }  // namespace
+
+// launchers of the two fused kernels for crm_sim.cu
+int crm_shard_pack_all(crm_sim* s, void* msg_lo, void* msg_hi, uint32_t* flags) {
+    if (!s->halo_sel_cap) return crm_fail(CRM_ERR_INVALID, "no halo selection yet (crm_sim_halo_pack_msgs with reselect)");
+    const uint32_t n_lo = msg_lo ? s->halo_sel_n[0] : 0, n_hi = msg_hi ? s->halo_sel_n[1] : 0;
+    const uint64_t threads = std::max<uint64_t>(1, (uint64_t)(n_lo + n_hi) * (s->lp + 5));
+    k_halo_pack_all<<<blocks_for(threads, 256), 256, 0, s->stream>>>(s->d, s->halo_sel[0], n_lo, s->halo_sel[1], n_hi, s->lp,
+                                                                     (uint32_t*)msg_lo, (uint32_t*)msg_hi, s->emax, s->skin, flags);
+    s->launches += 1;
+    return 0;
+}
+int crm_shard_unpack_all(crm_sim* s, const void* msg_lo, const void* msg_hi, const uint32_t* flags_all, int world,
+                         uint32_t* latch, uint32_t iteration_prev) {
+    if (s->n_ghost != s->ghost_n[0] + s->ghost_n[1])
+        return crm_fail(CRM_ERR_INVALID, "the ghosts of the last rebuild step include hand-over records: rebuild first");
+    const uint32_t n_lo = msg_lo ? s->ghost_n[0] : 0, n_hi = msg_hi ? s->ghost_n[1] : 0;
+    if ((s->ghost_n[0] && !msg_lo) || (s->ghost_n[1] && !msg_hi)) return crm_fail(CRM_ERR_INVALID, "missing halo message");
+    const uint64_t threads = std::max<uint64_t>(1, (uint64_t)(n_lo + n_hi) * (s->lp + 5));
+    k_ghost_unpack_all<<<blocks_for(threads, 256), 256, 0, s->stream>>>(s->d, (const uint32_t*)msg_lo, n_lo, (const uint32_t*)msg_hi,
+                                                                        n_hi, s->n, s->lp, flags_all, world, latch, iteration_prev);
+    s->launches += 1;
+    return 0;
+}
 
 extern "C" {
 

@@ -77,6 +77,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.pqe, 0, (size_t)cap * PL_QP * s->lp);
     G(s->d.pqs, 0, (size_t)cap * PL_QS * s->lp);
     G(s->d.pnq, 0, (size_t)cap * s->lp);
+    G(s->d.pslow, 0, (size_t)cap);
     G(s->d.vbuild, 0, (size_t)cap * s->lp);
     G(s->d.gof, 0, (size_t)cap);
     G(s->d.dcnt, 0, (size_t)cap);
@@ -248,6 +249,7 @@ void crm_fill_device_params(const crm_rod_params& p, PotParams& pot, MechParams&
 
 // what the (re)builds of the persistent structure reported about its rods; sticky until the next full build
 static void crm_note_list_flags(crm_sim* s) {
+    s->lists_maxl = std::max(s->lists_maxl, s->h_status->max_list);
     if (s->h_status->any_slow) s->lists_slow = true;
     if (s->h_status->seen_morse) s->lists_morse = true;
     if (s->h_status->seen_mie) s->lists_mie = true;
@@ -366,7 +368,7 @@ static int divisions_enqueue(crm_sim* s, uint32_t n_div, uint32_t n0, bool patch
     s->launches += 1;
     if (patch) {
         CK(cudaMemsetAsync(s->d.dirty_n, 0, sizeof(uint32_t), s->stream));
-        s->launches += launch_patch(s->d, n_div, n0, s->lp, s->lp > 8 ? 8 : 16, s->stream);
+        s->launches += launch_patch(s->d, n_div, n0, s->lp, s->lp > 8 ? 16 : 32, s->stream);
         CK(cudaMemcpyAsync(h_dirty, s->d.dirty_n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
     }
     CK(cudaGetLastError());
@@ -428,6 +430,8 @@ int crm_apply_divisions(crm_sim* s, const crm_ident* id_mother, const crm_ident*
     const uint32_t n0 = s->n, n_div = (uint32_t)s->h_div.size();
     int rc = crm_reserve(s, n0 + n_div);
     if (rc) return rc;
+    // (the list on the device does not survive a reallocation: the host's ordered copy goes back)
+    CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
     s->patch_divisions = false;  // (sharded runs search again after a division: it is a collective decision)
     if ((rc = divisions_enqueue(s, n_div, n0, false, nullptr))) return rc;
     if ((rc = crm_read_status(s))) return rc;
@@ -472,6 +476,8 @@ static int handle_divisions(crm_sim* s, uint32_t n_div) {
         // sort: order it through the host first
         if ((rc = fetch_divisions(s, n_div))) return rc;
         if ((rc = crm_reserve(s, n0 + n_div))) return rc;
+        // (the list on the device does not survive a reallocation: the host's ordered copy goes back)
+        CK(cudaMemcpyAsync(s->d.divlist, s->h_div.data(), sizeof(DivRecord) * n_div, cudaMemcpyHostToDevice, s->stream));
         const bool p2 = patch && !grow;
         if ((rc = divisions_enqueue(s, n_div, n0, p2, h_dirty))) return rc;
         if ((rc = crm_read_status(s))) return rc;
@@ -543,11 +549,22 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
     }
     s->launches += launch_binning(s->d, s->n_sims, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
-    if (build) s->lists_slow = s->lists_morse = s->lists_mie = false;  // until this step's status says otherwise (read before any list step)
+    if (build) {  // until this step's status says otherwise (read before any list step)
+        s->lists_slow = s->lists_morse = s->lists_mie = false;
+        s->lists_maxl = 0;
+    }
     launch_force(s->nv, s->d, s->fast_math, count, build, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
     s->launches += 1;
     return 0;
+}
+
+// list entries the list kernel stages per rod: the longest list of the live structure, rounded up to 4 (rows that
+// a division patched may have grown since the host last heard: the full capacity then)
+static void set_staging(crm_sim* s, bool rows_pending) {
+    const int cap = s->lp > 8 ? 16 : 32;
+    const int m = rows_pending ? cap : std::max(4, (int)(s->lists_maxl + 3u) / 4 * 4);
+    s->d.maxl = std::min(m, cap);
 }
 
 // force of a step between two rebuilds: no cell list, no search (k_force_eval)
@@ -558,6 +575,7 @@ static int launch_force_from_lists(crm_sim* s) {
     s->d.n = s->n + s->n_ghost;  // the build order covers the ghosts as well
     s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
+    set_staging(s, s->n_dirty != 0);
     if (s->n_dirty) {  // rows touched by the divisions of the last step: rebuilt with twice the skin as
         // margin, because their partners' displacement budgets keep counting from the last full build
         Dev dl = s->d;
@@ -755,6 +773,7 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
     uint32_t* const h_latch = reinterpret_cast<uint32_t*>(s->h_status + 1) + 24;  // pinned scratch behind the status
     const bool uniform = !s->lists_slow;
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
+    set_staging(s, false);
     for (uint32_t k = 0; k < B; ++k) {
         s->d.iteration = it0 + k + 1;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
@@ -1391,12 +1410,23 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
     uint32_t* const h_latch = reinterpret_cast<uint32_t*>(s->h_status + 1) + 24;
     const bool uniform = !s->lists_slow;
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
+    set_staging(s, false);
+    // Per step: ONE pack launch (both messages + the flags of the step just integrated), ONE NCCL group (halo
+    // send/recv + all-gather of those flags), ONE unpack launch (ghosts + the latch from the gathered flags of the
+    // previous step), force, integrate.  The flags of the last step are gathered behind the loop.
     int rc = 0;
+    uint32_t* const my_flags = s->flags_dev;
+    uint32_t* const all_flags = s->flags_dev + 4;
+    void* const slo = rank > 0 ? send_lo : nullptr;
+    void* const shi = rank + 1 < world ? send_hi : nullptr;
+    void* const rlo = rank > 0 ? recv_lo : nullptr;
+    void* const rhi = rank + 1 < world ? recv_hi : nullptr;
     for (uint32_t k = 0; k < B && !rc; ++k) {
         s->d.iteration = it0 + k + 1;
-        if ((rc = crm_sim_halo_repack(s, rank > 0 ? send_lo : nullptr, rank + 1 < world ? send_hi : nullptr))) break;
-        if ((rc = crm_comm_sendrecv(s->comm, send_lo, sl, recv_lo, rl, send_hi, sh, recv_hi, rh, s->stream))) break;
-        if ((rc = crm_sim_ghosts_refresh(s, rank > 0 ? recv_lo : nullptr, rank + 1 < world ? recv_hi : nullptr))) break;
+        // (k == 0: the status block has just been zeroed, the flags read "nothing happened")
+        if ((rc = crm_shard_pack_all(s, slo, shi, my_flags))) break;
+        if ((rc = crm_comm_exchange(s->comm, send_lo, sl, recv_lo, rl, send_hi, sh, recv_hi, rh, my_flags, all_flags, 16, s->stream))) break;
+        if ((rc = crm_shard_unpack_all(s, rlo, rhi, all_flags, world, s->latch_buf, (uint32_t)(it0 + k)))) break;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
         launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, s->stream);
         if (s->timers && k == 0) {
@@ -1405,10 +1435,13 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
         }
         launch_integrate(s->nv, s->d, s->stream);
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
-        k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, s->skin, 0u, s->flags_dev);
-        if ((rc = crm_comm_allgather(s->comm, s->flags_dev, s->flags_dev + 4, 16, s->stream))) break;
-        k_latch_from_flags<<<1, 32, 0, s->stream>>>(s->flags_dev + 4, world, s->latch_buf, (uint32_t)s->d.iteration);
-        s->launches += 4;
+        s->launches += 2;
+    }
+    if (!rc) {  // the flags of the last step (the host's copy; the latch of a full batch stays 0 unless it fired)
+        k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, s->skin, 0u, my_flags);
+        rc = crm_comm_allgather(s->comm, my_flags, all_flags, 16, s->stream);
+        k_latch_from_flags<<<1, 32, 0, s->stream>>>(all_flags, world, s->latch_buf, (uint32_t)(it0 + B));
+        s->launches += 2;
     }
     s->d.latch = nullptr;
     s->bounds_fresh = false;

@@ -73,6 +73,14 @@ int crm_comm_world(const crm_comm* c);
 int crm_comm_sendrecv(crm_comm* c, const void* send_lo, size_t n_send_lo, void* recv_lo, size_t n_recv_lo,
                       const void* send_hi, size_t n_send_hi, void* recv_hi, size_t n_recv_hi, cudaStream_t st);
 int crm_comm_allgather(crm_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+// both halo messages and the all-gather of the flags in ONE NCCL group (one launch)
+int crm_comm_exchange(crm_comm* c, const void* send_lo, size_t n_send_lo, void* recv_lo, size_t n_recv_lo, const void* send_hi,
+                      size_t n_send_hi, void* recv_hi, size_t n_recv_hi, const void* flags, void* flags_all,
+                      size_t flag_bytes, cudaStream_t st);
+// fused pack / unpack kernels of a sharded step between rebuilds (crm_shard.cu)
+int crm_shard_pack_all(crm_sim* s, void* msg_lo, void* msg_hi, uint32_t* flags);
+int crm_shard_unpack_all(crm_sim* s, const void* msg_lo, const void* msg_hi, const uint32_t* flags_all, int world,
+                         uint32_t* latch, uint32_t iteration_prev);
 void crm_comm_free(crm_comm* c);
 
 struct crm_sim {
@@ -98,6 +106,7 @@ struct crm_sim {
     bool need_rebuild = true;   // the next step must search (and rebuild the structure)
     bool have_lists = false;    // the structure on the device describes the current slots
     bool lists_morse = true, lists_mie = true;  // potential types among the rods of the structure (same protocol)
+    uint32_t lists_maxl = 32;   // longest list of the structure (sizes the staging area of the list kernel)
     bool lists_slow = true;     // ... and queues pairs with mixed potentials (known after the build step's status)
     bool want_rebuild = true;   // outcome of the last step: a local reason to rebuild (sharded runs: the
                                 // coordinator combines the slabs' wishes, crm_sim_keep_lists)
