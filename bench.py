@@ -571,7 +571,9 @@ def main():
     st = run.sim.step_stats()
     lists = run.sim.list_stats()
     lists = {"builds": lists["builds"] - stats0["builds"], "eval_steps": lists["eval_steps"] - stats0["eval_steps"],
-             "batches": st["batches"], "note": "inside the timed region"}
+             "batches": st["batches"], "note": "builds / eval_steps inside the timed region; the rest since the upload",
+             "overflows": lists.get("overflows"), "overflow_reasons": lists.get("overflow_reasons"),
+             "longest_list": lists.get("longest_list")}
     n = run.sim.n_rods
     run.sim.enable_timers(False)
 

@@ -8,8 +8,9 @@ from .cell_container import CellContainer, color_to_counter, counter_to_color
 from .datatypes import (AgentSettings, CellIdentifier, Configuration, GrowthRateSetter, MiePotentialF32,
                         MorsePotentialF32, PhysicalInteraction, RodAgent, RodMechanicsSettings,
                         SpringLengthThresholdSetter, StorageOption, VoxelPlainIndex)
-from .simulation import (SimulationError, generate_agents, generate_positions, run_simulation_with_agents,
-                         run_simulations_batched, sort_cellular_identifiers)
+from .simulation import (SimulationError, generate_agents, generate_positions, params_from_settings,
+                         run_simulation_with_agents, run_simulation_with_arrays, run_simulations_batched,
+                         sort_cellular_identifiers)
 
 # reference src/lib.rs:38-43,109-111
 MINUTE = 1.0

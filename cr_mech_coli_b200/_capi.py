@@ -164,6 +164,7 @@ class Library:
             "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
             "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
             "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
+            "sim_list_overflows": (C.c_int, [vp, P(u32), P(u64), P(u32)]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
             "sim_enable_timers": (C.c_int, [vp, C.c_int]),
             "sim_read_timers": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u64)]),
@@ -375,7 +376,12 @@ class Sim:
     def list_stats(self):
         b, e = C.c_uint64(0), C.c_uint64(0)
         self.L.check(self.L.fn("sim_list_stats")(self.h, C.byref(b), C.byref(e)))
-        return {"builds": int(b.value), "eval_steps": int(e.value)}
+        out = {"builds": int(b.value), "eval_steps": int(e.value)}
+        if self.L.has("sim_list_overflows"):
+            r, c, m = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
+            self.L.fn("sim_list_overflows")(self.h, C.byref(r), C.byref(c), C.byref(m))
+            out.update(overflows=int(c.value), overflow_reasons=int(r.value), longest_list=int(m.value))
+        return out
 
     def last_forces(self):
         f = np.zeros((self.n_rods, self.n_vertices, 3), dtype=np.float32)

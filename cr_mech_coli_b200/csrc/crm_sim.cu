@@ -559,11 +559,11 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
     return 0;
 }
 
-// list entries the list kernel stages per rod: the longest list of the live structure, rounded up to 4 (rows that
-// a division patched may have grown since the host last heard: the full capacity then)
+// list entries the list kernel stages per rod: the longest list of the live structure, rounded up to 4 (rows that a
+// division is about to patch grow by at most PATCH_EXTRA candidates before the host hears of their new length)
 static void set_staging(crm_sim* s, bool rows_pending) {
     const int cap = s->lp > 8 ? 16 : 32;
-    const int m = rows_pending ? cap : std::max(4, (int)(s->lists_maxl + 3u) / 4 * 4);
+    const int m = std::max(4, (int)(s->lists_maxl + (rows_pending ? (uint32_t)PATCH_EXTRA : 0u) + 3u) / 4 * 4);
     s->d.maxl = std::min(m, cap);
 }
 
@@ -685,6 +685,8 @@ static int step_conclude(crm_sim* s) {
         if (s->h_status->plist_overflow) {  // a rod did not fit: search every step for a while, then retry
             s->have_lists = false;
             s->holdoff = 64;
+            s->overflow_reasons |= s->h_status->plist_overflow;
+            s->n_overflows += 1;
         }
         if (s->h_status->patch_overflow) want = true;  // a patched row is full: a fresh search empties it
         const float disp = std::sqrt(__builtin_bit_cast(float, s->h_status->disp2_bits));
@@ -1029,6 +1031,16 @@ int crm_sim_set_skin(crm_sim* s, float skin) {
     if (s->n) return fail(CRM_ERR_INVALID, "set the skin before the agents");
     s->skin = skin;
     s->need_rebuild = true;
+    return 0;
+}
+
+// Why builds of the neighbour structure were abandoned: reason bits (1 more than 32 / 16 neighbour rods, 2 / 4 more
+// than 32 queued own / ext evaluations per vertex, 8 more than 8 sensing candidates per vertex), how often, and the
+// longest list of the live structure.
+int crm_sim_list_overflows(const crm_sim* s, uint32_t* reasons, uint64_t* count, uint32_t* longest_list) {
+    if (reasons) *reasons = s->overflow_reasons;
+    if (count) *count = s->n_overflows;
+    if (longest_list) *longest_list = s->lists_maxl;
     return 0;
 }
 

@@ -106,6 +106,8 @@ struct crm_sim {
     bool need_rebuild = true;   // the next step must search (and rebuild the structure)
     bool have_lists = false;    // the structure on the device describes the current slots
     bool lists_morse = true, lists_mie = true;  // potential types among the rods of the structure (same protocol)
+    uint32_t overflow_reasons = 0;  // why builds were abandoned (bits of Status::plist_overflow), how often
+    uint64_t n_overflows = 0;
     uint32_t lists_maxl = 32;   // longest list of the structure (sizes the staging area of the list kernel)
     bool lists_slow = true;     // ... and queues pairs with mixed potentials (known after the build step's status)
     bool want_rebuild = true;   // outcome of the last step: a local reason to rebuild (sharded runs: the

@@ -90,6 +90,43 @@ def run_simulation_with_agents(config: Configuration, agents, device: int = 0) -
     return CellContainer(path=path, _snapshots=snaps)
 
 
+def params_from_settings(agent_settings: AgentSettings, n: int) -> np.ndarray:
+    """``n`` parameter records (``crm_rod_params``) filled from one ``AgentSettings`` template: the array form of
+    ``[RodAgent(pos=p, vel=v, **agent_settings.to_rod_agent_dict()) for ...]`` without building the objects."""
+    m = agent_settings.mechanics
+    template = RodAgent(np.zeros((2, 3), np.float32), np.zeros((2, 3), np.float32),
+                        PhysicalInteraction(agent_settings.interaction), m.diffusion_constant, m.spring_tension, m.rigidity,
+                        m.spring_length, m.damping, agent_settings.growth_rate, agent_settings.growth_rate_setter,
+                        agent_settings.spring_length_threshold, agent_settings.spring_length_threshold_setter,
+                        agent_settings.neighbor_reduction)
+    rec = np.zeros(1, _capi.ROD_PARAMS_DTYPE)
+    template._to_record(rec[0])
+    return np.repeat(rec, int(n))
+
+
+def run_simulation_with_arrays(config: Configuration, pos, vel, params, device: int = 0) -> CellContainer:
+    """``run_simulation_with_agents`` for colonies too large to hold as Python objects (extension; no reference
+    counterpart): positions / velocities ``(n_rods, n_vertices, 3)`` f32 and one ``crm_rod_params`` record per rod
+    (``params_from_settings``, or ``_capi.ROD_PARAMS_DTYPE`` filled by hand) in, the same ``CellContainer`` out.
+    The container keeps its snapshots packed, so a 1e6-rod run never materialises a million ``RodAgent`` objects
+    unless a caller asks for them (``positions_at_iteration`` returns the arrays)."""
+    storage.check_options(config.storage_options)
+    lib = _capi.product()
+    pos = np.ascontiguousarray(pos, dtype=np.float32)
+    vel = np.ascontiguousarray(vel, dtype=np.float32)
+    params = np.ascontiguousarray(params, dtype=_capi.ROD_PARAMS_DTYPE)
+    with _capi.Sim(lib, config._to_c(), device) as sim:
+        sim.set_agents(pos, vel, params)
+        sim.run()
+        snaps = [_Snapshot(*s) for s in sim.snapshots()]
+    path = None
+    if StorageOption.SerdeJson in config.storage_options:
+        path = storage.new_run_directory(config)
+        for s in snaps:
+            storage.write_snapshot(path, s.iteration, s.pos, s.vel, s.par, s.ids, s.parents)
+    return CellContainer(path=path, _snapshots=snaps)
+
+
 def run_simulations_batched(config: Configuration, agent_lists, device: int = 0):
     """Many independent ``run_simulation_with_agents(config, agents)`` calls in ONE device state
     (parameter-fitting ensembles: reference src/crm_fit/predict.rs:231-287 run once per parameter

@@ -224,6 +224,10 @@ int crm_sim_read_step_stats(crm_sim* sim, double* integrate_ms, uint64_t* integr
 int crm_sim_set_skin(crm_sim* sim, float skin);
 /* Steps that rebuilt the structure / steps that reused it. */
 int crm_sim_list_stats(const crm_sim* sim, uint64_t* n_builds, uint64_t* n_eval_steps);
+/* Builds abandoned because a rod did not fit the structure's capacities: reason bits (1: more than 32 neighbour
+ * rods (16 for 9..16 vertices), 2 / 4: more than 32 queued own / ext evaluations per vertex, 8: more than 8
+ * sensing candidates per vertex), their number, and the longest list of the live structure. */
+int crm_sim_list_overflows(const crm_sim* sim, uint32_t* reasons, uint64_t* count, uint32_t* longest_list);
 /* Divisions while the structure is live do not force a new search: the rows of the daughters and of the
  * mothers' neighbours are rebuilt from candidate lists (the reference re-sorts its voxels every step;
  * cellular_raza chili update_cell_cycle + sort_cells_in_subdomains).  Count of division steps absorbed

@@ -126,3 +126,19 @@ def test_serde_json_storage_round_trip(product_lib, tmp_path):
     config.storage_suffix = "trial-7"
     cc2 = crm_shim.run_simulation_with_agents(config, agents)
     assert cc2.path.name == "trial-7" and (cc2.path / "cells" / "json").is_dir()
+
+
+def test_run_simulation_with_arrays_equals_the_object_api(product_lib):
+    """The packed entry point (colonies too large for a list of RodAgent objects) returns the container the object
+    API returns."""
+    config = crm.Configuration(t_max=30.0, n_saves=2)
+    s = crm.AgentSettings(growth_rate=0.03)
+    positions = crm.generate_positions(6, s, config, rng_seed=2)
+    agents = [crm.RodAgent(pos=p, vel=p * 0.0, **s.to_rod_agent_dict()) for p in positions]
+    a = crm.run_simulation_with_agents(config, agents)
+    pos = np.stack(positions)
+    b = crm.run_simulation_with_arrays(config, pos, np.zeros_like(pos), crm.params_from_settings(s, len(pos)))
+    assert a.get_all_iterations() == b.get_all_iterations()
+    assert a.get_parent_map() == b.get_parent_map()
+    for it in a.get_all_iterations():
+        assert np.array_equal(a.positions_at_iteration(it), b.positions_at_iteration(it))

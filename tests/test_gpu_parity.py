@@ -627,3 +627,29 @@ def test_batched_steps_report_errors_at_the_same_iteration(product_lib):
         g.close()
     assert msgs[0][:2] == msgs[1][:2], msgs
     assert msgs[0][1] >= 3 and msgs[0][2] and not msgs[1][2], msgs
+
+
+def test_lists_with_more_than_16_partners(product_lib):
+    """A stacked 3-D colony whose rods list up to 32 neighbours within cutoff + skin (the multilayer runs of
+    reference cr_mech_coli/crm_multilayer/runner.py:14-79 do): the persistent structure holds them (5-bit list
+    index), list steps are used, and the trajectory equals the oracle's and a run that searches every step."""
+    pos, L, H = multilayer_colony(360, spacing=(25.0, 5.2), layer_height=4.6)
+    cfg = _capi.make_config(domain_size=(L, L), domain_height=H, n_voxels=(max(1, int(L // 40)),) * 2, dt=0.025,
+                            t_max=1.5, n_saves=2, gel_pressure=0.1, surface_friction=0.03, surface_friction_distance=0.3)
+    par = multilayer_params(len(pos), diffusion_constant=0.0, growth_rate=0.0)
+    par["spring_length_threshold"] = 1e30
+    g, o = _pair(cfg, pos, par, product_lib)
+    g.run()
+    o.run()
+    st = g.list_stats()
+    assert st["longest_list"] > 16 and st["overflows"] == 0, st
+    assert st["eval_steps"] >= 40, st
+    for (it, pg, vg, parg, *_), (_, po, vo, paro, *_) in zip(g.snapshots(), o.snapshots()):
+        assert np.abs(pg - po).max() < TRAJ_ATOL, f"iteration {it}: {np.abs(pg - po).max()}"
+        assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
+    with _capi.Sim(product_lib, cfg) as h:
+        h.set_skin(0.0)
+        h.set_agents(pos, np.zeros_like(pos), par)
+        h.run()
+        ph = h.snapshots()[-1][1]
+    assert np.abs(g.snapshots()[-1][1] - ph).max() < 1e-4
