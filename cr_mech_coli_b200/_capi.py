@@ -160,6 +160,8 @@ class Library:
             "sim_set_exact_math": (C.c_int, [vp, C.c_int]),
             "sim_set_skin": (C.c_int, [vp, C.c_float]),
             "sim_set_batching": (C.c_int, [vp, C.c_int]),
+            "sim_set_fused": (C.c_int, [vp, C.c_int]),
+            "sim_fused_steps": (u64, [vp]),
             "sim_read_step_stats": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u32)]),
             "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
             "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
@@ -359,6 +361,13 @@ class Sim:
 
     def set_spring_end_weight(self, w: float):
         self.L.check(self.L.fn("sim_set_spring_end_weight")(self.h, float(w)))
+
+    def set_fused(self, on: bool):
+        """List steps as one kernel (forces + mechanics, default) or as two launches."""
+        self.L.check(self.L.fn("sim_set_fused")(self.h, int(on)))
+
+    def fused_steps(self) -> int:
+        return int(self.L.fn("sim_fused_steps")(self.h))
 
     def set_batching(self, on: bool):
         """List steps in batches with a device-side latch (default) or one host round trip per step."""

@@ -72,6 +72,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.bsphere, on, (size_t)cap);
     G(s->d.chord, 2 * on, (size_t)2 * cap);
     G(s->d.vrec, on * s->lp, (size_t)cap * s->lp);
+    G(s->vrec_alt, 0, (size_t)cap * s->lp);
     G(s->d.plist, 0, (size_t)cap * PL_MAXP_MAX);
     G(s->d.pqo, 0, (size_t)cap * PL_QP * s->lp);
     G(s->d.pqe, 0, (size_t)cap * PL_QP * s->lp);
@@ -567,6 +568,11 @@ static void set_staging(crm_sim* s, bool rows_pending) {
     s->d.maxl = std::min(m, cap);
 }
 
+// the list step can run force + mechanics in ONE kernel (k_force_eval<.., FUSE>): fast math, no mixed pairs
+static bool fusable(const crm_sim* s) { return s->fused && s->fast_math && !s->lists_slow; }
+// after a fused step the buffer it wrote holds the current vertex records
+static void swap_vrec(crm_sim* s) { std::swap(s->d.vrec, s->vrec_alt); }
+
 // force of a step between two rebuilds: no cell list, no search (k_force_eval)
 static int launch_force_from_lists(crm_sim* s) {
     s->d.emax_limit_bits = 0u;
@@ -576,6 +582,7 @@ static int launch_force_from_lists(crm_sim* s) {
     s->d.n_own = s->n;
     CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
     set_staging(s, s->n_dirty != 0);
+    const bool rows_rebuilt = s->n_dirty != 0;
     if (s->n_dirty) {  // rows touched by the divisions of the last step: rebuilt with twice the skin as
         // margin, because their partners' displacement budgets keep counting from the last full build
         Dev dl = s->d;
@@ -587,8 +594,12 @@ static int launch_force_from_lists(crm_sim* s) {
         s->n_dirty = 0;
     }
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
-    launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow,
-                      s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE), s->stream);
+    const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
+    // force + mechanics in one kernel unless rows were rebuilt in front of it (a row that did not fit keeps the
+    // force the rebuild computed: it needs the stand-alone integrator)
+    s->step_fused = fusable(s) && !rows_rebuilt;
+    if (s->step_fused) s->d.vrec_out = s->vrec_alt;
+    launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow, pt, s->step_fused, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
     s->launches += 1;
     return 0;
@@ -661,9 +672,15 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
     }
     if (rc) return rc;
     s->steps_since_build += 1;
-    launch_integrate(s->nv, s->d, s->stream);
+    if (use_lists && s->step_fused) {
+        swap_vrec(s);
+        s->n_fused_steps += 1;
+    } else {
+        launch_integrate(s->nv, s->d, s->stream);
+        s->launches += 1;
+    }
+    s->step_fused = false;
     s->bounds_fresh = false;
-    s->launches += 1;
     if (dev_flags) {
         k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, persistent(s) ? s->skin : 0.0f, s->have_lists ? 0u : 1u, dev_flags);
         s->launches += 1;
@@ -776,19 +793,23 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
     const bool uniform = !s->lists_slow;
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
     set_staging(s, false);
+    const bool fuse = fusable(s);
     for (uint32_t k = 0; k < B; ++k) {
         s->d.iteration = it0 + k + 1;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
-        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, s->stream);
-        if (s->timers && k == 0) {
-            CK(cudaEventRecord(s->ev1, s->stream));
-            CK(cudaEventRecord(s->ev2, s->stream));
+        if (fuse) s->d.vrec_out = s->vrec_alt;
+        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, fuse, s->stream);
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev1, s->stream));
+        if (fuse) {
+            swap_vrec(s);
+        } else {
+            if (s->timers && k == 0) CK(cudaEventRecord(s->ev2, s->stream));
+            launch_integrate(s->nv, s->d, s->stream);
+            if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
         }
-        launch_integrate(s->nv, s->d, s->stream);
-        if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
     }
     s->d.latch = nullptr;
-    s->launches += 2ull * B;
+    s->launches += (fuse ? 1ull : 2ull) * B;
     s->bounds_fresh = false;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
@@ -798,6 +819,10 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
     const uint32_t stop = *h_latch;
     const uint32_t n_done = stop ? (uint32_t)(stop - (uint32_t)it0) : B;
     if (n_done == 0 || n_done > B) return fail(CRM_ERR_CUDA, "batched steps: latch out of range (%u of %u)", n_done, B);
+    if (fuse) {  // the steps behind the latch wrote nothing: the records of the last executed step are current
+        if ((B - n_done) & 1u) swap_vrec(s);
+        s->n_fused_steps += n_done;
+    }
     s->iteration = it0 + n_done;
     s->d.iteration = s->iteration;
     s->rod_steps += (uint64_t)s->n * n_done;
@@ -811,9 +836,11 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         s->force_ms += ms;
         s->force_launches += 1;
-        CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
-        s->integrate_ms += ms;
-        s->integrate_launches += 1;
+        if (!fuse) {
+            CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+            s->integrate_ms += ms;
+            s->integrate_launches += 1;
+        }
     }
     *done = n_done;
     return step_conclude(s);
@@ -980,6 +1007,7 @@ int crm_sim_create(const crm_config* c, int device, crm_sim** out) {
     CK(cudaEventCreateWithFlags(&s->ev_status, cudaEventDisableTiming));
     if (const char* bt = getenv("CRM_B200_BATCH")) s->batching = bt[0] != '0';
     if (const char* ab = getenv("CRM_B200_ASYNC_BOUNDS")) s->async_bounds = ab[0] != '0';
+    if (const char* fu = getenv("CRM_B200_FUSED")) s->fused = fu[0] != '0';
     s->d.lx = c->domain_size[0];
     s->d.ly = c->domain_size[1];
     s->d.lz = c->domain_height;
@@ -1035,7 +1063,7 @@ int crm_sim_set_skin(crm_sim* s, float skin) {
 }
 
 // Why builds of the neighbour structure were abandoned: reason bits (1 more than 32 / 16 neighbour rods, 2 / 4 more
-// than 32 queued own / ext evaluations per vertex, 8 more than 8 sensing candidates per vertex), how often, and the
+// than 64 queued own / ext evaluations per vertex, 8 more than 8 sensing candidates per vertex), how often, and the
 // longest list of the live structure.
 int crm_sim_list_overflows(const crm_sim* s, uint32_t* reasons, uint64_t* count, uint32_t* longest_list) {
     if (reasons) *reasons = s->overflow_reasons;
@@ -1423,6 +1451,8 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
     const bool uniform = !s->lists_slow;
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
     set_staging(s, false);
+    const bool fuse = fusable(s);
+    uint32_t swaps = 0;
     // Per step: ONE pack launch (both messages + the flags of the step just integrated), ONE NCCL group (halo
     // send/recv + all-gather of those flags), ONE unpack launch (ghosts + the latch from the gathered flags of the
     // previous step), force, integrate.  The flags of the last step are gathered behind the loop.
@@ -1440,14 +1470,18 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
         if ((rc = crm_comm_exchange(s->comm, send_lo, sl, recv_lo, rl, send_hi, sh, recv_hi, rh, my_flags, all_flags, 16, s->stream))) break;
         if ((rc = crm_shard_unpack_all(s, rlo, rhi, all_flags, world, s->latch_buf, (uint32_t)(it0 + k)))) break;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
-        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, s->stream);
-        if (s->timers && k == 0) {
-            CK(cudaEventRecord(s->ev1, s->stream));
-            CK(cudaEventRecord(s->ev2, s->stream));
+        if (fuse) s->d.vrec_out = s->vrec_alt;
+        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, fuse, s->stream);
+        if (s->timers && k == 0) CK(cudaEventRecord(s->ev1, s->stream));
+        if (fuse) {
+            swap_vrec(s);
+            ++swaps;
+        } else {
+            if (s->timers && k == 0) CK(cudaEventRecord(s->ev2, s->stream));
+            launch_integrate(s->nv, s->d, s->stream);
+            if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
         }
-        launch_integrate(s->nv, s->d, s->stream);
-        if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
-        s->launches += 2;
+        s->launches += fuse ? 1 : 2;
     }
     if (!rc) {  // the flags of the last step (the host's copy; the latch of a full batch stays 0 unless it fired)
         k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, s->skin, 0u, my_flags);
@@ -1467,6 +1501,10 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
     const uint32_t stop = *h_latch;
     const uint32_t n_done = stop ? (uint32_t)(stop - (uint32_t)it0) : B;
     if (n_done == 0 || n_done > B) return fail(CRM_ERR_CUDA, "sharded steps: latch out of range (%u of %u)", n_done, B);
+    if (fuse) {
+        if ((swaps - n_done) & 1u) swap_vrec(s);
+        s->n_fused_steps += n_done;
+    }
     s->iteration = it0 + n_done;
     s->d.iteration = s->iteration;
     s->rod_steps += (uint64_t)s->n * n_done;
@@ -1480,9 +1518,11 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
         CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         s->force_ms += ms;
         s->force_launches += 1;
-        CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
-        s->integrate_ms += ms;
-        s->integrate_launches += 1;
+        if (!fuse) {
+            CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+            s->integrate_ms += ms;
+            s->integrate_launches += 1;
+        }
     }
     *done = n_done;
     memcpy(flags_out, s->flags_host, sizeof(uint32_t) * 4 * world);
@@ -1574,6 +1614,8 @@ int crm_sim_compute_forces(crm_sim* s, float* out_force, uint32_t* out_nn) {
 // Interaction forces the last step used ([n][n_vertices][3]); tests compare them with a fresh search.
 int crm_sim_last_forces(crm_sim* s, float* out_force) {
     if (!s || !out_force) return fail(CRM_ERR_INVALID, "null argument");
+    if (s->fused && s->n_fused_steps)
+        return fail(CRM_ERR_INVALID, "fused list steps do not store their forces: crm_sim_set_fused(sim, 0) before stepping");
     CK(cudaSetDevice(s->device));
     if (s->n == 0) return 0;
     launch_pack(s->nv, s->d.force, s->stage, s->n, s->stream);
@@ -1651,6 +1693,15 @@ int crm_sim_read_step_stats(crm_sim* s, double* integrate_ms, uint64_t* integrat
     if (batch_len) *batch_len = s->batch_len;
     return 0;
 }
+
+// 1 (default): a list step is ONE kernel (forces + mechanics, the force never goes to memory); 0: k_force_eval and
+// k_integrate as two launches (crm_sim_last_forces then returns the forces of the last step).
+int crm_sim_set_fused(crm_sim* s, int on) {
+    if (!s) return fail(CRM_ERR_INVALID, "null sim");
+    s->fused = on != 0;
+    return 0;
+}
+uint64_t crm_sim_fused_steps(const crm_sim* s) { return s ? s->n_fused_steps : 0; }
 
 // 1 (default): list steps are enqueued in batches with a device-side latch; 0: one host round trip per step.
 int crm_sim_set_batching(crm_sim* s, int on) {

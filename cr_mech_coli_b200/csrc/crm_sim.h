@@ -36,7 +36,7 @@ void launch_pack(int nv, const float* src, float* dst, uint32_t n, cudaStream_t 
 void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
 int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st);
 void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
-void launch_force_eval(int nv, const Dev& d, bool fast, bool uniform, int pot_type, cudaStream_t st);
+bool launch_force_eval(int nv, const Dev& d, bool fast, bool uniform, int pot_type, bool fused, cudaStream_t st);
 void launch_force_lists(int nv, const Dev& d, bool fast, cudaStream_t st);
 int launch_patch(const Dev& d, uint32_t n_div, uint32_t n0, int lp, int maxp, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
@@ -92,6 +92,10 @@ struct crm_sim {
     uint32_t n_ghost = 0;     // ghost rods in slots [n, n + n_ghost)
     uint32_t ncells_cap = 0;
     crm::Dev d{};
+    float4* vrec_alt = nullptr;  // second vertex-record buffer of the fused list step (swapped with d.vrec per step)
+    bool step_fused = false;     // the list step in flight runs the fused kernel
+    bool fused = true;           // list steps run force + mechanics in one kernel (CRM_B200_FUSED=0 / crm_sim_set_fused)
+    uint64_t n_fused_steps = 0;
     char* arena = nullptr;   // the one device allocation all per-rod arrays are parts of (crm_reserve)
     float* stage = nullptr;  // boundary-layout staging buffer [cap][nv][3]
     float* stage2 = nullptr; // second one: positions and velocities cross the bus back to back

@@ -214,6 +214,13 @@ int crm_sim_set_spring_end_weight(crm_sim* sim, float weight);
  * round trip per step.  crm_sim_read_step_stats: integrator time next to crm_sim_read_timers' force time (both
  * sampled on the first step of every batch), batches run, current batch length. */
 int crm_sim_set_batching(crm_sim* sim, int on);
+/* A list step (between two searches) is ONE kernel by default: the interaction forces are summed in registers and
+ * the mechanics of the rod (RodMechanics::calculate_increment, Adams-Bashforth, update_cycle, boundary) follow at
+ * once, so the force array is neither written nor read.  0 restores the two launches (needed for
+ * crm_sim_last_forces).  Env CRM_B200_FUSED=0 sets the default.  Mixed-potential colonies and exact-math runs
+ * always use two launches. */
+int crm_sim_set_fused(crm_sim* sim, int on);
+uint64_t crm_sim_fused_steps(const crm_sim* sim);
 int crm_sim_read_step_stats(crm_sim* sim, double* integrate_ms, uint64_t* integrate_launches, uint64_t* n_batches,
                             uint32_t* batch_len);
 
@@ -225,7 +232,7 @@ int crm_sim_set_skin(crm_sim* sim, float skin);
 /* Steps that rebuilt the structure / steps that reused it. */
 int crm_sim_list_stats(const crm_sim* sim, uint64_t* n_builds, uint64_t* n_eval_steps);
 /* Builds abandoned because a rod did not fit the structure's capacities: reason bits (1: more than 32 neighbour
- * rods (16 for 9..16 vertices), 2 / 4: more than 32 queued own / ext evaluations per vertex, 8: more than 8
+ * rods (16 for 9..16 vertices), 2 / 4: more than 64 queued own / ext evaluations per vertex, 8: more than 8
  * sensing candidates per vertex), their number, and the longest list of the live structure. */
 int crm_sim_list_overflows(const crm_sim* sim, uint32_t* reasons, uint64_t* count, uint32_t* longest_list);
 /* Divisions while the structure is live do not force a new search: the rows of the daughters and of the

@@ -77,6 +77,7 @@ def test_pinned_buffers_round_trip(product_lib):
     par["en"][::7] = 5.0  # the constant cache must follow every change of (en, em, cutoff)
     par["cutoff"][::5] = 5.5
     a = _capi.Sim(product_lib, cfg)
+    a.set_fused(False)  # (last_forces: the fused list step keeps its forces in registers)
     a.set_agents(pos, np.zeros_like(pos), par)
     a.step(3)
     ref = a.get_state()
@@ -89,6 +90,7 @@ def test_pinned_buffers_round_trip(product_lib):
            product_lib.pinned_empty(n, _capi.ROD_PARAMS_DTYPE), product_lib.pinned_empty(n, _capi.IDENT_DTYPE),
            product_lib.pinned_empty(n, _capi.IDENT_DTYPE))
     b = _capi.Sim(product_lib, cfg)
+    b.set_fused(False)
     b.set_agents(*pp)
     b.step(3)
     got = b.get_state(out=out)

@@ -185,7 +185,7 @@ def test_persistent_lists_match_search_every_step(product_lib):
     o.set_agents(pos, vel, par)
     o.step(steps)
     po, vo = o.get_state()[:2]
-    assert out[0.0][1] == {"builds": 0, "eval_steps": 0}
+    assert (out[0.0][1]["builds"], out[0.0][1]["eval_steps"]) == (0, 0)
     assert out[0.5][1]["eval_steps"] > steps // 2 and out[0.5][1]["builds"] >= 2
     assert out[0.1][1]["builds"] > out[0.5][1]["builds"]
     for skin in (0.0, 0.5, 0.1):
@@ -313,6 +313,7 @@ def test_divisions_patch_the_live_neighbour_structure(product_lib):
     assert np0 == 0 and np1 >= 10, (np0, np1)
     # the interaction forces of a list step right after patched divisions equal a fresh search of the same state
     g = _capi.Sim(product_lib, cfg)
+    g.set_fused(False)  # (last_forces: the fused list step keeps its forces in registers)
     g.set_agents(pos, np.zeros_like(pos), par)
     g.step(6)
     assert g.patch_count() >= 4
@@ -653,3 +654,60 @@ def test_lists_with_more_than_16_partners(product_lib):
         h.run()
         ph = h.snapshots()[-1][1]
     assert np.abs(g.snapshots()[-1][1] - ph).max() < 1e-4
+
+
+# ---- the fused list step (forces + mechanics in one kernel) ---------------------------------------------------
+
+@pytest.mark.parametrize("case", ["lattice_mie", "growth_morse", "multilayer_wiener", "nv5"])
+def test_fused_list_step_equals_two_launches(product_lib, case):
+    """k_force_eval<.., FUSE> runs integrate_rod on the force it has just summed: the same arithmetic as k_force_eval
+    + k_integrate, so the two ways of stepping end bit-identical; and both follow the oracle."""
+    if case == "lattice_mie":
+        n = 3000
+        L = lattice_domain(n)
+        cfg = _capi.make_config(domain_size=(L, L), n_voxels=(1, 1), dt=0.01, t_max=1.5, n_saves=1)
+        pos = lattice_colony(n, seed=21)
+        par = mie_params(n, growth_rate=0.0)
+        par["spring_length_threshold"] = 1e30
+        vel = np.zeros_like(pos)
+        vel[:, :, 0] = 0.6
+    elif case == "growth_morse":
+        n, L = 36, 400.0
+        cfg = _capi.make_config(domain_size=(L, L), n_voxels=(3, 3), t_max=24.0, dt=0.1, n_saves=3)
+        pos = lattice_colony(n, spacing=(60.0, 40.0), margin=40.0, seed=11, angle_std=0.5)
+        par = morse_params(n, growth_rate=0.08)
+        par["growth_rate"] = np.random.default_rng(4).uniform(0.05, 0.1, n)
+        vel = np.zeros_like(pos)
+    elif case == "multilayer_wiener":
+        cfg, pos = _stochastic_colony()
+        par = multilayer_params(len(pos), diffusion_constant=0.03, growth_rate=0.01)
+        par["spring_length_threshold"] = np.random.default_rng(5).uniform(3.05, 3.6, len(par)).astype(np.float32)
+        vel = np.zeros_like(pos)
+    else:
+        n, L = 300, 260.0
+        cfg = _capi.make_config(domain_size=(L, L), n_voxels=(2, 2), dt=0.02, t_max=2.0, n_saves=1)
+        pos = lattice_colony(n, domain=L, n_vertices=5, spring_length=5.0, seed=3)
+        par = morse_params(n, radius=1.5, cutoff=6.0, growth_rate=0.0)
+        par["spring_length_threshold"] = 1e30
+        vel = np.random.default_rng(1).normal(0, 0.05, pos.shape).astype(np.float32)
+    runs = []
+    for fused in (True, False):
+        with _capi.Sim(product_lib, cfg) as g:
+            g.set_fused(fused)
+            g.set_agents(pos, vel, par)
+            g.run()
+            runs.append((g.snapshots(), g.fused_steps(), g.list_stats()))
+    (a, fa, la), (b, fb, lb) = runs
+    assert fa > 10 and fb == 0, (fa, fb)
+    assert la["builds"] == lb["builds"] and la["eval_steps"] == lb["eval_steps"]
+    for sa, sb in zip(a, b):
+        assert sa[0] == sb[0]
+        for x, y in zip(sa[1:], sb[1:]):
+            assert x.tobytes() == y.tobytes()
+    with oracle.sim(cfg) as o:
+        o.set_agents(pos, vel, par)
+        o.run()
+        so = o.snapshots()
+    for (it, pg, *_r), (_, po, *_q) in zip(a, so):
+        assert pg.shape == po.shape
+        assert np.abs(pg - po).max() < (TRAJ_ATOL if case != "growth_morse" or it <= 140 else 1e-2), (it, np.abs(pg - po).max())
