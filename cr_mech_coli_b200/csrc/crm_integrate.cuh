@@ -53,8 +53,16 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
         X1[c] = newx[i]; V1[c] = newv[i]; X2[c] = oldx[i]; V2[c] = oldv[i];
     }
     const int nh = d.nhist[a];
-    const CycleParams cp = d.cyc[a];
-    const float nnb = cp.has_nr ? (nn_count >= 0 ? (float)nn_count : (float)d.nn[a]) : 0.0f;
+    // the cold cycle record (48 B) is read only by rods whose growth depends on their neighbour count
+    // (GrowState.w flags them); the setters in it matter at divisions only (k_divide)
+    const bool has_nr = gs.w != 0.0f;
+    float nr_max = 1.0f, nr_exp = 0.0f, nnb = 0.0f;
+    if (has_nr) {
+        const CycleParams cp = d.cyc[a];
+        nr_max = (float)cp.nr_max;
+        nr_exp = cp.nr_exp;
+        nnb = nn_count >= 0 ? (float)nn_count : (float)d.nn[a];
+    }
     float4 vb = make_float4(0.f, 0.f, 0.f, 0.f);
     if (d.vbuild) vb = d.vbuild[(size_t)a * LP + li];
     const bool iso = d.sim_fail != nullptr;
@@ -153,9 +161,9 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
     }
     // Cycle::update_cycle (bit-exact ops: no FMA contraction, same order as the reference)
     float rate = gs.x;
-    if (cp.has_nr) {
-        const float mx = (float)cp.nr_max;
-        rate = __fmul_rn(gs.x, powf(fmaxf(__fdiv_rn(__fsub_rn(mx, nnb), mx), 0.0f), cp.nr_exp));
+    if (has_nr) {
+        const float mx = nr_max;
+        rate = __fmul_rn(gs.x, powf(fmaxf(__fdiv_rn(__fsub_rn(mx, nnb), mx), 0.0f), nr_exp));
     }
     const float newL = __fadd_rn(L, __fmul_rn(__fmul_rn(rate, dt), L));
     bool dividing = newL > gs.y && !frozen;

@@ -365,8 +365,8 @@ __global__ void __launch_bounds__(128) k_divide(Dev d, uint32_t n_div, uint32_t 
         const float g2 = setter_sample(cp.growth_kind, cp.growth_a, cp.growth_b, 1, d.seed, d.iteration, key, 0);
         const float l1 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 0, d.seed, d.iteration, key, 1);
         const float l2 = setter_sample(cp.thr_kind, cp.thr_a, cp.thr_b, 1, d.seed, d.iteration, key, 1);
-        d.grow[a] = make_float4(g1, l1, newL, 0.f);
-        d.grow[b] = make_float4(g2, l2, newL, 0.f);
+        d.grow[a] = make_float4(g1, l1, newL, gs.w);
+        d.grow[b] = make_float4(g2, l2, newL, gs.w);
         d.pot[b] = pot;
         d.mech[b] = d.mech[a];
         d.cyc[b] = cp;

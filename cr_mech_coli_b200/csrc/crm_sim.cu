@@ -229,7 +229,7 @@ static void fill_device_params_cached(const crm_rod_params& p, ParamCache& k, Po
         pot.d = k.d;
     }
     mech = make_float4(p.spring_tension, p.rigidity, p.damping, p.diffusion_constant);
-    grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, 0.0f);
+    grow = make_float4(p.growth_rate, p.spring_length_threshold, p.spring_length, p.has_neighbor_reduction ? 1.0f : 0.0f);
     memset(&cyc, 0, sizeof(cyc));
     cyc.growth_kind = p.growth_setter_kind;
     cyc.growth_a = p.growth_setter_a;
