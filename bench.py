@@ -575,6 +575,19 @@ def main():
              "overflows": lists.get("overflows"), "overflow_reasons": lists.get("overflow_reasons"),
              "longest_list": lists.get("longest_list")}
     n = run.sim.n_rods
+    fused_steps = run.sim.fused_steps()
+    # the same steps as two launches (k_force_eval + k_integrate), a few of them outside the timed region: what
+    # the force part and the mechanics part of the fused kernel cost on their own
+    two_launch = None
+    if fused_steps and not run.slabs:
+        run.sim.set_fused(False)
+        run.sim.enable_timers(True)
+        run.step(8)
+        t2, s2 = run.sim.read_timers(), run.sim.step_stats()
+        run.sim.set_fused(True)
+        if t2["force_launches"] and s2["integrate_launches"]:
+            two_launch = {"force_ms": t2["force_ms"] / t2["force_launches"],
+                          "integrate_ms": s2["integrate_ms"] / s2["integrate_launches"]}
     run.sim.enable_timers(False)
 
     # ---- C3: 100 warm-up + 1000 timed steps, rebuild steps inside the region, and the cost of one
@@ -686,13 +699,14 @@ def main():
         "halo": halo,
         "neighbour_lists": lists,
         "clocks": clocks,
-        "step_breakdown_ms": {"force": force_ms, "integrate": integ_ms,
-                              "idle_or_other": (ms / K - force_ms - integ_ms) if integ_ms is not None else None,
+        "step_breakdown_ms": {"force": force_ms, "integrate": integ_ms, "fused": bool(fused_steps),
+                              "idle_or_other": (ms / K - force_ms - (integ_ms or 0.0)) if (integ_ms is not None or fused_steps) else None,
                               "note": "force / integrate: CUDA events around the first launch of every batch (list steps) or "
                                       "every launch (single steps); the rest of ms_per_step is gaps between kernels, rebuild "
                                       "work, memsets and the status copy"},
-        "roofline": {"kernel": "k_force_eval<8,1> on list steps, k_force<8,1,0,1> on the rebuild steps "
-                               "(event time averaged over both)", "bound": "fp32", "achieved": achieved, "peak": fp32.value,
+        "roofline": {"kernel": ("k_force_eval<.., FUSE>: interaction forces + mechanics of a list step in ONE launch" if fused_steps
+                                else "k_force_eval on list steps, k_force<BUILD> on the rebuild steps (event time averaged over both)"),
+                     "fused": bool(fused_steps), "bound": "fp32", "achieved": achieved, "peak": fp32.value,
                      "unit": "TFLOP/s", "frac": achieved / fp32.value if fp32.value else None,
                      "traffic": ncu_traffic() if name == "c3" else None,
                      "peak_source": "crm_microbench FFMA loop on this device (FP32 non-tensor peak is not in "
@@ -702,11 +716,21 @@ def main():
                      "force_ms_per_launch": force_ms, "force_share_of_step": force_ms / (ms / K),
                      "ordered_pairs_in_cutoff": pairs["pairs_in_cutoff"],
                      "candidate_pairs_evaluated": pairs["pairs_tested"],
-                     "flop_per_eval": FLOP_PER_EVAL[w["pot"]], "evals_per_ordered_pair": EVALS_PER_ORDERED_PAIR},
-        "roofline_mech": {"kernels": "k_integrate (plus binning on rebuild steps): everything but the force kernel", "bound": "hbm",
-                          "achieved": n * MECH_BYTES_PER_ROD_STEP / ((integ_ms or mech_ms) * 1e-3) * 1e-9 if (integ_ms or mech_ms) > 0 else None,
-                          "peak": peaks["hbm_gbs"], "unit": "GB/s", "peak_source": peaks_src,
-                          "ms_per_launch": integ_ms, "ms_per_step_all_but_force": mech_ms},
+                     "flop_per_eval": FLOP_PER_EVAL[w["pot"]], "evals_per_ordered_pair": EVALS_PER_ORDERED_PAIR,
+                     "note": "achieved = algorithmic FLOP of the interaction forces / duration of the launch; the fused launch also "
+                             "carries the mechanics (HBM side: roofline_mech), so its FP32 fraction is below the force-only one "
+                             "(two_launch_reference)",
+                     "two_launch_reference": (dict(two_launch, frac_fp32=flops / (two_launch["force_ms"] * 1e-3) * 1e-12 / fp32.value)
+                                              if two_launch and fp32.value else None)},
+        "roofline_mech": ({"kernels": "the same fused launch, read as a memory kernel: SURVEY's 836 algorithmic B/rod-step of the "
+                                      "mechanics over the WHOLE launch duration (the force part hides it)", "bound": "hbm",
+                           "achieved": n * MECH_BYTES_PER_ROD_STEP / (force_ms * 1e-3) * 1e-9, "peak": peaks["hbm_gbs"],
+                           "unit": "GB/s", "peak_source": peaks_src, "ms_per_launch": force_ms,
+                           "mechanics_cost_ms": (force_ms - two_launch["force_ms"]) if two_launch else None} if fused_steps else
+                          {"kernels": "k_integrate (plus binning on rebuild steps): everything but the force kernel", "bound": "hbm",
+                           "achieved": n * MECH_BYTES_PER_ROD_STEP / ((integ_ms or mech_ms) * 1e-3) * 1e-9 if (integ_ms or mech_ms) > 0 else None,
+                           "peak": peaks["hbm_gbs"], "unit": "GB/s", "peak_source": peaks_src,
+                           "ms_per_launch": integ_ms, "ms_per_step_all_but_force": mech_ms}),
     }
     if line["roofline_mech"]["achieved"]:
         line["roofline_mech"]["frac"] = line["roofline_mech"]["achieved"] / peaks["hbm_gbs"]
