@@ -211,6 +211,7 @@ class Library:
                                          vp, P(C.c_double)]),
             "overlap": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, P(C.c_float)]),
             "parents_diff_mask": (C.c_int, [vp, vp, u64, vp, u32, vp, u32, C.c_float, vp, P(C.c_int64)]),
+            "overlap_noalloc": (C.c_int, [vp, vp, u32, u32, C.c_float, C.c_float, vp, vp, vp]),
             "comm_unique_id": (C.c_int, [vp]),
             "comm_create": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, P(vp)]),
             "comm_destroy": (None, [vp]),

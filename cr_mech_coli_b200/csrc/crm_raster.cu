@@ -9,6 +9,8 @@
 // (bitmaps: 8 B of atomics + 6 B of output per pixel); nothing here is a contraction.
 // Compiled with --fmad=false: the outline arithmetic follows the reference's f32 operations one by one
 // and the trigonometric functions go through f64 (cos_rn): outlines equal the CPU oracle's bit for bit.
+#include <mutex>
+
 #include "crm_sim.h"
 
 using crm::blocks_for;
@@ -583,3 +585,85 @@ int crm_parents_diff_mask(const uint8_t* mask1, const uint8_t* mask2, uint64_t n
 }
 
 }  // extern "C"
+
+// ---- crm_overlap_noalloc: overlap() for callers that cannot allocate (CUDA graph capture, serving loops) ----
+// No counterpart in the reference.  The scratch of the outline and
+// area kernels (what crm_overlap takes from cudaMalloc) lives in ONE file-scope device array; every GPU that
+// loads the library holds it until exit.  All calls share it and it keeps the last call's contents: the words that
+// must start at zero are cleared on the stream at the start of every call, and calls that overlap on the GPU race.
+namespace {
+
+constexpr uint32_t NOALLOC_MAX_RODS = CRM_NOALLOC_MAX_RODS;
+// parts, each 256-B aligned: hull [rods][MAXV] float2 | bbox [rods] float4 | count [rods] int | orient [rods] f32 |
+// total (f64) | status (int)
+constexpr size_t NA_HULL = 0;
+constexpr size_t NA_BBOX = NA_HULL + sizeof(float2) * MAXV * NOALLOC_MAX_RODS;
+constexpr size_t NA_COUNT = NA_BBOX + sizeof(float4) * NOALLOC_MAX_RODS;
+constexpr size_t NA_ORIENT = NA_COUNT + sizeof(int) * NOALLOC_MAX_RODS;
+constexpr size_t NA_TOTAL = NA_ORIENT + sizeof(float) * NOALLOC_MAX_RODS;
+constexpr size_t NA_STATUS = NA_TOTAL + 256;
+constexpr size_t NA_BYTES = NA_STATUS + 256;
+static_assert(NA_BBOX % 256 == 0 && NA_COUNT % 256 == 0 && NA_ORIENT % 256 == 0 && NA_TOTAL % 256 == 0, "parts stay aligned");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the kernels get is
+// looked up once per device, with that device current.
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[NA_MAX_DEVICES] = {};
+std::mutex g_noalloc_mutex;
+
+int noalloc_scratch(unsigned char** out) {
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NA_MAX_DEVICES) return crm_fail(CRM_ERR_INVALID, "crm_overlap_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+// status of the outlines as crm_overlap reports it (0, CRM_ERR_NOMEM, CRM_ERR_NUMERIC) and the area, f64 -> f32
+__global__ void k_noalloc_finish(const double* __restrict__ total, const int* __restrict__ status, float* __restrict__ out_area,
+                                 int* __restrict__ out_status) {
+    const int h = *status;
+    *out_area = (float)*total;
+    *out_status = h <= -0x40000000 ? CRM_ERR_NOMEM : h < 0 ? CRM_ERR_NUMERIC : 0;
+}
+
+}  // namespace
+
+extern "C" int crm_overlap_noalloc(const float* d_pos, const float* d_radii, uint32_t n, uint32_t n_vertices, float delta_angle,
+                                   float epsilon, float* d_out_area, int32_t* d_out_status, void* stream) {
+    if (!d_pos || !d_radii || !d_out_area || !d_out_status) return crm_fail(CRM_ERR_INVALID, "null argument");
+    if (n_vertices < 2) return crm_fail(CRM_ERR_INVALID, "an outline needs two vertices");
+    if (n > NOALLOC_MAX_RODS)
+        return crm_fail(CRM_ERR_INVALID, "crm_overlap_noalloc: %u rods exceed the fixed scratch of %u rods (use crm_overlap)", n,
+                        NOALLOC_MAX_RODS);
+    if (crm_device_count() <= 0) return crm_fail(CRM_ERR_CUDA, "no CUDA device available (cr_mech_coli_b200 has no CPU fallback)");
+    unsigned char* base = nullptr;
+    int rc = noalloc_scratch(&base);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float2* hull = reinterpret_cast<float2*>(base + NA_HULL);
+    float4* bbox = reinterpret_cast<float4*>(base + NA_BBOX);
+    int* count = reinterpret_cast<int*>(base + NA_COUNT);
+    float* orient = reinterpret_cast<float*>(base + NA_ORIENT);
+    double* total = reinterpret_cast<double*>(base + NA_TOTAL);
+    int* status = reinterpret_cast<int*>(base + NA_STATUS);
+    // total | status must start at zero (the array keeps the last call's contents); hull / bbox / count / orient of
+    // rods 0..n-1 are written by k_hull before k_overlap reads them
+    CK(cudaMemsetAsync(total, 0, 512, st));
+    if (n) {
+        k_hull<<<blocks_for(n, 64), 64, 0, st>>>(d_pos, d_radii, (int)n, (int)n_vertices, delta_angle, epsilon, 1.0f, 1.0f, 1, 1, hull,
+                                                  nullptr, count, bbox, nullptr, orient, status);
+        k_overlap<<<blocks_for((uint64_t)n * 32, 128), 128, 0, st>>>(hull, count, bbox, orient, (int)n, total);
+    }
+    k_noalloc_finish<<<1, 1, 0, st>>>(total, status, d_out_area, d_out_status);
+    CK(cudaGetLastError());
+    return 0;
+}

@@ -414,6 +414,19 @@ int crm_parents_diff_mask(const uint8_t* mask1, const uint8_t* mask2, uint64_t n
                           uint32_t n_counters, const int32_t* parent_of, uint32_t n_cells, float parent_penalty,
                           float* out, int64_t* missing_pixel);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  `crm_overlap` without
+ * any allocation: d_pos [n][n_vertices][3] f32, d_radii [n] f32, d_out_area (1 f32) and d_out_status (1 i32: 0,
+ * CRM_ERR_NUMERIC "lines should be intersecting" or CRM_ERR_NOMEM "outline too long") are DEVICE pointers of the
+ * current device; the kernels are enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call returns
+ * without waiting.  The scratch (outlines, boxes, accumulator: 2.1 MB) is a fixed device array inside the library that
+ * every GPU loading it holds until exit; n > CRM_NOALLOC_MAX_RODS is rejected with CRM_ERR_INVALID.  Calls neither
+ * cudaMalloc / cudaFree nor any allocating library routine.  All calls share the scratch: calls that overlap on
+ * the GPU (different streams, no ordering between them) race. */
+#define CRM_NOALLOC_MAX_RODS 1024u
+int crm_overlap_noalloc(const float* d_pos, const float* d_radii, uint32_t n, uint32_t n_vertices, float delta_angle,
+                        float epsilon, float* d_out_area, int32_t* d_out_status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
