@@ -498,6 +498,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=4)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-long-run", action="store_true")
+    ap.add_argument("--relax", type=int, default=2000, help="c4: untimed relaxation steps before the second timing")
     ap.add_argument("--no-strong", action="store_true")
     ap.add_argument("--e2e-reps", type=int, default=3)
     args = ap.parse_args()
@@ -573,7 +574,8 @@ def main():
     lists = {"builds": lists["builds"] - stats0["builds"], "eval_steps": lists["eval_steps"] - stats0["eval_steps"],
              "batches": st["batches"], "note": "builds / eval_steps inside the timed region; the rest since the upload",
              "overflows": lists.get("overflows"), "overflow_reasons": lists.get("overflow_reasons"),
-             "longest_list": lists.get("longest_list")}
+             "longest_list": lists.get("longest_list"),
+             "rebuild_reasons_since_upload": lists.get("rebuild_reasons")}
     n = run.sim.n_rods
     fused_steps = run.sim.fused_steps()
     # the same steps as two launches (k_force_eval + k_integrate), a few of them outside the timed region: what
@@ -605,6 +607,23 @@ def main():
                     "value": n * world * 1000 / (ms_long * 1e-3),
                     "builds": b1["builds"] - b0["builds"], "eval_steps": b1["eval_steps"] - b0["eval_steps"],
                     "rebuild_step_ms": rebuild_ms}
+
+    # ---- C4: the stacked-lattice start state is far from mechanical equilibrium (damping 0.02: a vertex moves
+    # beyond skin/2 in nearly every step, so nearly every step searches).  The same K steps timed again after
+    # `--relax` untimed steps, with the reasons for the searches, show what a settled colony costs.
+    relaxed = None
+    if name == "c4" and args.relax > 0 and not args.no_long_run:
+        r0 = run.sim.list_stats()
+        run.step(args.relax)
+        r1 = run.sim.list_stats()
+        ms_r = reduce_max([timed_steps(run, lib, 10 * K, barrier)])[0]
+        r2_ = run.sim.list_stats()
+        diff = lambda a, b, k: {q: b[k][q] - a[k][q] for q in b[k]} if k in b else None
+        relaxed = {"relax_steps": args.relax, "steps": 10 * K, "ms_per_step": ms_r / (10 * K),
+                   "value": run.sim.n_rods * world * 10 * K / (ms_r * 1e-3), "rods_rank0": int(run.sim.n_rods),
+                   "builds": r2_["builds"] - r1["builds"], "eval_steps": r2_["eval_steps"] - r1["eval_steps"],
+                   "rebuild_reasons": diff(r1, r2_, "rebuild_reasons"),
+                   "rebuild_reasons_while_relaxing": diff(r0, r1, "rebuild_reasons")}
 
     check = parity_check(run, lib, world, rank, dist, torch) if run.slabs else None
     run.close()
@@ -741,6 +760,8 @@ def main():
         line["growth"] = {"steps_to_target": grow_steps, "rods_at_start_of_timed_region": int(rod_steps // K)}
     if long_run:
         line["long_run"] = long_run
+    if relaxed:
+        line["relaxed"] = relaxed
     if strong:
         line["strong"] = strong
     if check:

@@ -165,6 +165,7 @@ class Library:
             "sim_read_step_stats": (C.c_int, [vp, P(C.c_double), P(u64), P(u64), P(u32)]),
             "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
             "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
+            "sim_rebuild_reasons": (C.c_int, [vp, C.c_uint64 * 8]),
             "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
             "sim_list_overflows": (C.c_int, [vp, P(u32), P(u64), P(u32)]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
@@ -391,6 +392,11 @@ class Sim:
             r, c, m = C.c_uint32(0), C.c_uint64(0), C.c_uint32(0)
             self.L.fn("sim_list_overflows")(self.h, C.byref(r), C.byref(c), C.byref(m))
             out.update(overflows=int(c.value), overflow_reasons=int(r.value), longest_list=int(m.value))
+        if self.L.has("sim_rebuild_reasons"):
+            w = (C.c_uint64 * 8)()
+            self.L.fn("sim_rebuild_reasons")(self.h, w)
+            out["rebuild_reasons"] = dict(zip(("displacement", "left_slab", "list_overflow", "patch_overflow",
+                                               "unpatched_divisions", "no_lists", "grid_redo", "steps"), map(int, w)))
         return out
 
     def last_forces(self):

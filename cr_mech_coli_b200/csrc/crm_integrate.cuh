@@ -16,6 +16,46 @@ __device__ __forceinline__ bool reflect(float& p, float& v, float hi) {
     return p >= 0.0f && p <= hi;
 }
 
+// What a rod's mechanics read of its own state: loaded from the arrays by k_integrate (load_mech_global), staged
+// through shared memory by the fused list step (crm_force.cu: cp.async at kernel start, so that the round trip to
+// HBM runs under the force loops instead of stalling the tail).
+struct MechIn {
+    float V[3], X1[3], V1[3], X2[3], V2[3];  // velocity, newer and older stored increment (dx, dv)
+    MechParams mp;
+    GrowState gs;
+    float4 vb;  // vertex record at the last build of the neighbour structure (zero if there is none)
+    int nh;     // stored increments so far
+};
+
+// increment history as a two-slot ring: `newx/newv` were written at step it-1, `oldx/oldv` at step it-2 (read as
+// the older increment, then rewritten by this step)
+struct HistPtrs { float *newx, *newv, *oldx, *oldv; };
+__device__ __forceinline__ HistPtrs hist_ptrs(const Dev& d) {
+    const bool odd = (d.iteration & 1ull) != 0;
+    return HistPtrs{odd ? d.dx2 : d.dx1, odd ? d.dv2 : d.dv1, odd ? d.dx1 : d.dx2, odd ? d.dv1 : d.dv2};
+}
+
+template <int NV>
+__device__ __forceinline__ void load_mech_global(const Dev& d, const uint32_t a, const int l, MechIn& m) {
+    constexpr int LP = Lay<NV>::LP;
+    constexpr int STRIDE = Lay<NV>::STRIDE;
+    const size_t o = (size_t)a * STRIDE;
+    const int li = l < NV ? l : 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) m.V[c] = d.vel[o + c * LP + li];
+    m.mp = d.mech[a];
+    m.gs = d.grow[a];
+    const HistPtrs h = hist_ptrs(d);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const size_t i = o + c * LP + li;
+        m.X1[c] = h.newx[i]; m.V1[c] = h.newv[i]; m.X2[c] = h.oldx[i]; m.V2[c] = h.oldv[i];
+    }
+    m.nh = d.nhist[a];
+    m.vb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (d.vbuild) m.vb = d.vbuild[(size_t)a * LP + li];
+}
+
 // fused mechanics: RodMechanics::calculate_increment + Adams-Bashforth(3) + Cycle::update_cycle
 // + boundary + bounding sphere of the new state.
 // Body shared by k_integrate (crm_mech.cu: P and F come from the pos / force arrays) and by the fused list step
@@ -24,35 +64,28 @@ __device__ __forceinline__ bool reflect(float& p, float& v, float hi) {
 // (shuffles run over gm), `valid` lanes store.  `skip_step`: a step of a batch behind the one that latched,
 // tested behind the loads so that they are all in flight first.  `nn_count` < 0: the neighbour count is read from
 // d.nn.  The new vertex record goes to `vrec_out` (the fused step must not overwrite records other blocks
-// are still reading as neighbours).  Every TU that includes this is compiled with --fmad=false.
+// are still reading as neighbours).  `m`: the rod's own state (every load of the step is issued before the first
+// store: the stores below may alias as far as the compiler knows, and one DRAM round trip per vector component is
+// what bounds k_integrate).  Every TU that includes this is compiled with --fmad=false.
 template <int NV>
 __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, const int l, const bool valid, const unsigned gm,
                                               const float (&P)[3], const float (&F)[3], const bool skip_step,
-                                              const int nn_count, float4* __restrict__ vrec_out) {
+                                              const int nn_count, float4* __restrict__ vrec_out, const MechIn& m) {
     constexpr int LP = Lay<NV>::LP;
     constexpr int STRIDE = Lay<NV>::STRIDE;
     const size_t o = (size_t)a * STRIDE;
     const bool hv = valid && l < NV;
-    const int li = l < NV ? l : 0;
-    float V[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) V[c] = d.vel[o + c * LP + li];
-    const MechParams mp = d.mech[a];
-    GrowState gs = d.grow[a];
-    // every load of the step is issued here, before the first store (the stores below may alias as far
-    // as the compiler knows, and one DRAM round trip per vector component is what bounds this kernel)
-    const bool odd = (d.iteration & 1ull) != 0;
-    float* const newx = odd ? d.dx2 : d.dx1;  // increment history as a two-slot ring: written at step it-1
-    float* const newv = odd ? d.dv2 : d.dv1;
-    float* const oldx = odd ? d.dx1 : d.dx2;  // written at step it-2: read as the older increment, rewritten now
-    float* const oldv = odd ? d.dv1 : d.dv2;
-    float X1[3], V1[3], X2[3], V2[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const size_t i = o + c * LP + li;
-        X1[c] = newx[i]; V1[c] = newv[i]; X2[c] = oldx[i]; V2[c] = oldv[i];
-    }
-    const int nh = d.nhist[a];
+    const float (&V)[3] = m.V;
+    const float (&X1)[3] = m.X1;
+    const float (&V1)[3] = m.V1;
+    const float (&X2)[3] = m.X2;
+    const float (&V2)[3] = m.V2;
+    const MechParams mp = m.mp;
+    GrowState gs = m.gs;
+    const HistPtrs hp = hist_ptrs(d);
+    float* const oldx = hp.oldx;
+    float* const oldv = hp.oldv;
+    const int nh = m.nh;
     // the cold cycle record (48 B) is read only by rods whose growth depends on their neighbour count
     // (GrowState.w flags them); the setters in it matter at divisions only (k_divide)
     const bool has_nr = gs.w != 0.0f;
@@ -63,8 +96,7 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
         nr_exp = cp.nr_exp;
         nnb = nn_count >= 0 ? (float)nn_count : (float)d.nn[a];
     }
-    float4 vb = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (d.vbuild) vb = d.vbuild[(size_t)a * LP + li];
+    const float4 vb = m.vb;
     const bool iso = d.sim_fail != nullptr;
     const uint32_t sim_a = iso ? d.tile[a] : 0u;
     const bool frozen = iso && d.sim_fail[sim_a] != 0;

@@ -197,7 +197,9 @@ __global__ void __launch_bounds__(128) k_integrate(Dev d) {
         P[c] = d.pos[o + c * LP + li];
         F[c] = d.force[o + c * LP + li];
     }
-    integrate_rod<NV>(d, a, l, valid, 0xffffffffu, P, F, (stop != 0u && stop < (unsigned)d.iteration) || skip != 0u, -1, d.vrec);
+    MechIn m;
+    load_mech_global<NV>(d, a, l, m);
+    integrate_rod<NV>(d, a, l, valid, 0xffffffffu, P, F, (stop != 0u && stop < (unsigned)d.iteration) || skip != 0u, -1, d.vrec, m);
 }
 
 // ------------------------------------------------------------------------------------

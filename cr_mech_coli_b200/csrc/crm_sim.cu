@@ -2,11 +2,39 @@
 // include/crm_b200.h.  Replaces the run_main! driver of the reference
 // (src/simulation.rs:234-319): save schedule, per-step kernel sequence, division
 // bookkeeping (CellIdentifier / parent assignment), snapshots.
+#include <chrono>
+#include <mutex>
+
 #include "crm_sim.h"
 
 using namespace crm;
 
 static thread_local std::string g_err;
+
+// CRM_B200_TRACE=1: wall-clock phases of the upload / download entry points on stderr (diagnostics only)
+static bool trace_on() {
+    static const bool on = [] { const char* e = getenv("CRM_B200_TRACE"); return e && *e && *e != '0'; }();
+    return on;
+}
+struct Trace {
+    const char* what;
+    std::chrono::steady_clock::time_point t0, t;
+    std::string line;
+    explicit Trace(const char* w) : what(w) { if (trace_on()) t0 = t = std::chrono::steady_clock::now(); }
+    void mark(const char* phase) {
+        if (!trace_on()) return;
+        const auto now = std::chrono::steady_clock::now();
+        char buf[96];
+        snprintf(buf, sizeof buf, " %s %.2f", phase, std::chrono::duration<double, std::milli>(now - t).count());
+        line += buf;
+        t = now;
+    }
+    ~Trace() {
+        if (!trace_on()) return;
+        fprintf(stderr, "[crm trace] %s:%s | total %.2f ms\n", what, line.c_str(),
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
+};
 
 int crm_fail(int code, const char* fmt, ...) {
     char buf[1024];
@@ -34,6 +62,70 @@ static void parallel_for(size_t n, F f) {
     f((size_t)0, std::min(n, chunk));
     for (auto& t : th) t.join();
 }
+
+// Process-wide page-locked staging for the parameter blocks of upload / download: converted records cross the bus
+// from (into) it at link speed and asynchronously, which pageable std::vectors never do (the driver bounces them
+// through its own small pinned buffer, ~3x slower, and blocks the host meanwhile).  One buffer, grown on demand
+// up to POOL_LIMIT and kept until the process ends (cudaHostAlloc costs ~0.3 ms/MB: paid once, not per sim); a
+// call that finds it in use by another thread, or needs more than the limit, falls back to pageable memory.
+namespace {
+constexpr size_t POOL_LIMIT = (size_t)1 << 30;
+struct PinnedPool {
+    std::mutex m;
+    char* p = nullptr;
+    size_t cap = 0;
+    bool busy = false;
+} g_pool;
+struct PinnedLease {
+    char* p = nullptr;
+    bool pooled = false;
+    crm_hvec<char> pageable;
+    explicit PinnedLease(size_t bytes) {
+        if (bytes <= POOL_LIMIT) {
+            std::lock_guard<std::mutex> lock(g_pool.m);
+            if (!g_pool.busy) {
+                if (g_pool.cap < bytes) {
+                    if (g_pool.p) cudaFreeHost(g_pool.p);
+                    g_pool.p = nullptr;
+                    g_pool.cap = 0;
+                    const size_t want = (bytes + (bytes >> 3) + ((size_t)1 << 20) - 1) >> 20 << 20;
+                    void* q = nullptr;
+                    if (cudaHostAlloc(&q, want, cudaHostAllocPortable) == cudaSuccess) {
+                        g_pool.p = static_cast<char*>(q);
+                        g_pool.cap = want;
+                    } else {
+                        cudaGetLastError();
+                    }
+                }
+                if (g_pool.cap >= bytes) {
+                    g_pool.busy = true;
+                    pooled = true;
+                    p = g_pool.p;
+                }
+            }
+        }
+        if (!pooled) {
+            pageable.resize(bytes + 256);
+            p = pageable.data() + ((256 - (reinterpret_cast<uintptr_t>(pageable.data()) & 255)) & 255);
+        }
+    }
+    ~PinnedLease() {
+        if (pooled) {
+            std::lock_guard<std::mutex> lock(g_pool.m);
+            g_pool.busy = false;
+        }
+    }
+    PinnedLease(const PinnedLease&) = delete;
+    PinnedLease& operator=(const PinnedLease&) = delete;
+    // carve `count` items of T (256-B aligned parts)
+    template <class T> T* take(size_t& off, size_t count) {
+        T* r = reinterpret_cast<T*>(p + off);
+        off += (sizeof(T) * count + 255) / 256 * 256;
+        return r;
+    }
+    template <class T> static size_t part(size_t count) { return (sizeof(T) * count + 255) / 256 * 256; }
+};
+}  // namespace
 
 // All per-rod arrays live in ONE device allocation (an arena): a colony of 1e6 rods needs ~45 arrays, and 45
 // cudaMalloc calls cost more than moving the colony across the bus (they dominated the upload of the end-to-end
@@ -595,9 +687,10 @@ static int launch_force_from_lists(crm_sim* s) {
     }
     if (s->timers) CK(cudaEventRecord(s->ev0, s->stream));
     const int pt = s->lists_morse == s->lists_mie ? -1 : (s->lists_mie ? CRM_POT_MIE : CRM_POT_MORSE);
-    // force + mechanics in one kernel unless rows were rebuilt in front of it (a row that did not fit keeps the
-    // force the rebuild computed: it needs the stand-alone integrator)
-    s->step_fused = fusable(s) && !rows_rebuilt;
+    // force + mechanics in one kernel, also when rows were rebuilt in front of it (a row that did not fit keeps
+    // the force the rebuild computed: the fused kernel integrates such a rod with that force)
+    s->step_fused = fusable(s);
+    (void)rows_rebuilt;
     if (s->step_fused) s->d.vrec_out = s->vrec_alt;
     launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow, pt, s->step_fused, s->stream);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
@@ -698,21 +791,34 @@ static int step_conclude(crm_sim* s) {
     if ((rc = crm_report_device_error(s))) return rc;
     const uint32_t n_div = s->h_status->n_div;
     bool want = s->h_status->n_leave > 0;
+    s->why_rebuild[7] += 1;
+    if (want) s->why_rebuild[1] += 1;
     if (persistent(s)) {
+        if (!s->have_lists) s->why_rebuild[5] += 1;
         if (s->h_status->plist_overflow) {  // a rod did not fit: search every step for a while, then retry
             s->have_lists = false;
             s->holdoff = 64;
             s->overflow_reasons |= s->h_status->plist_overflow;
             s->n_overflows += 1;
+            s->why_rebuild[2] += 1;
         }
-        if (s->h_status->patch_overflow) want = true;  // a patched row is full: a fresh search empties it
+        if (s->h_status->patch_overflow) {  // a patched row is full: a fresh search empties it
+            want = true;
+            s->why_rebuild[3] += 1;
+        }
         const float disp = std::sqrt(__builtin_bit_cast(float, s->h_status->disp2_bits));
-        if (!(disp < 0.4999f * s->skin)) want = true;
+        if (!(disp < 0.4999f * s->skin)) {
+            want = true;
+            if (s->have_lists) s->why_rebuild[0] += 1;
+        }
     }
     // divisions alone do not force a new search while the structure is live: its rows are patched
     s->patch_divisions = n_div > 0 && !want && persistent(s) && s->have_lists && !s->need_rebuild && !s->sharded &&
                          s->patching;
-    if (n_div > 0 && !s->patch_divisions) want = true;
+    if (n_div > 0 && !s->patch_divisions) {
+        if (!want && persistent(s) && s->have_lists) s->why_rebuild[4] += 1;
+        want = true;
+    }
     s->want_rebuild = want || !s->have_lists;
     // sharded runs rebuild in all slabs at once: the coordinator clears the flag (crm_sim_keep_lists)
     if (s->sharded || s->want_rebuild) s->need_rebuild = true;
@@ -746,6 +852,7 @@ static int step_finish(crm_sim* s) {
             s->iteration -= 1;
             s->rod_steps -= s->n;
             s->n_grid_redos += 1;
+            s->why_rebuild[6] += 1;
             s->need_rebuild = true;
             s->have_lists = false;
             s->bounds_fresh = true;  // (k_bounds ran on the current positions and s->emax is its result)
@@ -880,11 +987,24 @@ static int advance(crm_sim* s, uint64_t n_steps) {
     return 0;
 }
 
-static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par) {
+static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par, crm_ident* ids = nullptr,
+                          crm_ident* parents = nullptr) {
     const size_t m = (size_t)s->n * s->nv * 3;
     if (s->n == 0) return 0;
-    // everything is enqueued first (two staging buffers), ONE wait; into pinned caller buffers the copies
-    // run at bus speed while nothing else blocks
+    Trace tr("download_state");
+    // Everything is enqueued first, the small parameter blocks in front: the host threads merge them into the
+    // caller's records while the positions and velocities (two staging buffers) are still crossing the bus; into
+    // pinned caller buffers those copies run at link speed.
+    const size_t np_ = par ? s->n : 0;
+    PinnedLease lease(PinnedLease::part<GrowState>(np_) + PinnedLease::part<uint32_t>(np_));
+    size_t off = 0;
+    GrowState* const g = lease.take<GrowState>(off, np_);
+    uint32_t* const nn = lease.take<uint32_t>(off, np_);
+    if (par) {
+        CK(cudaMemcpyAsync(g, s->d.grow, sizeof(GrowState) * s->n, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(nn, s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaEventRecord(s->ev_status, s->stream));
+    }
     if (pos) {
         launch_pack(s->nv, s->d.pos, s->stage, s->n, s->stream);
         CK(cudaMemcpyAsync(pos, s->stage, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
@@ -893,14 +1013,17 @@ static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* pa
         launch_pack(s->nv, s->d.vel, s->stage2, s->n, s->stream);
         CK(cudaMemcpyAsync(vel, s->stage2, sizeof(float) * m, cudaMemcpyDeviceToHost, s->stream));
     }
-    crm_hvec<GrowState> g(par ? s->n : 0);
-    crm_hvec<uint32_t> nn(par ? s->n : 0);
-    if (par) {
-        CK(cudaMemcpyAsync(g.data(), s->d.grow, sizeof(GrowState) * s->n, cudaMemcpyDeviceToHost, s->stream));
-        CK(cudaMemcpyAsync(nn.data(), s->d.nn, sizeof(uint32_t) * s->n, cudaMemcpyDeviceToHost, s->stream));
+    tr.mark("enqueue");
+    if (ids || parents) {  // host-only bookkeeping: copied while the device data is on its way
+        parallel_for(s->n, [&](size_t a0, size_t a1) {
+            if (ids) memcpy(ids + a0, s->ids.data() + a0, sizeof(crm_ident) * (a1 - a0));
+            if (parents) memcpy(parents + a0, s->parents.data() + a0, sizeof(crm_ident) * (a1 - a0));
+        });
+        tr.mark("ids");
     }
-    CK(cudaStreamSynchronize(s->stream));
     if (par) {
+        CK(cudaEventSynchronize(s->ev_status));
+        tr.mark("wait_params");
         parallel_for(s->n, [&](size_t a0, size_t a1) {
             for (size_t a = a0; a < a1; ++a) {
                 par[a] = s->base[a];
@@ -910,7 +1033,10 @@ static int download_state(crm_sim* s, float* pos, float* vel, crm_rod_params* pa
                 par[a].n_neighbors = nn[a];
             }
         });
+        tr.mark("merge");
     }
+    CK(cudaStreamSynchronize(s->stream));
+    tr.mark("wait");
     return 0;
 }
 
@@ -1063,12 +1189,18 @@ int crm_sim_set_skin(crm_sim* s, float skin) {
 }
 
 // Why builds of the neighbour structure were abandoned: reason bits (1 more than 32 / 16 neighbour rods, 2 / 4 more
-// than 64 queued own / ext evaluations per vertex, 8 more than 8 sensing candidates per vertex), how often, and the
+// than 128 queued own / ext evaluations per vertex, 8 more than 8 sensing candidates per vertex), how often, and the
 // longest list of the live structure.
 int crm_sim_list_overflows(const crm_sim* s, uint32_t* reasons, uint64_t* count, uint32_t* longest_list) {
     if (reasons) *reasons = s->overflow_reasons;
     if (count) *count = s->n_overflows;
     if (longest_list) *longest_list = s->lists_maxl;
+    return 0;
+}
+
+int crm_sim_rebuild_reasons(const crm_sim* s, uint64_t out[8]) {
+    if (!s || !out) return fail(CRM_ERR_INVALID, "null argument");
+    for (int k = 0; k < 8; ++k) out[k] = s->why_rebuild[k];
     return 0;
 }
 
@@ -1116,8 +1248,10 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->nv = (int)nv;
     s->lp = lanes_per_rod((int)nv);
     s->n = 0;
+    Trace tr("set_agents");
     int rc = crm_reserve(s, std::max<uint32_t>(n + n / 4 + 16, 1024));
     if (rc) return rc;
+    tr.mark("reserve");
     s->iteration = 0;
     s->snaps.clear();
     std::fill(s->vox_counter.begin(), s->vox_counter.end(), 0);
@@ -1144,40 +1278,59 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         CK(cudaMemcpyAsync(s->stage2, vel, sizeof(float) * m, cudaMemcpyHostToDevice, s->stream));
         launch_unpack(s->nv, s->stage2, s->d.vel, n, s->stream);
     }
-    crm_hvec<PotParams> pot(n);
-    crm_hvec<MechParams> mech(n);
-    crm_hvec<GrowState> grow(n);
-    crm_hvec<CycleParams> cyc(n);
-    crm_hvec<uint32_t> nn(n);
+    tr.mark("host_vectors+enqueue_pos_vel");
+    // converted records are staged page-locked and leave in chunks: the copy of chunk k runs while the host
+    // threads convert chunk k+1 (and behind the positions / velocities enqueued above)
+    PinnedLease lease(PinnedLease::part<PotParams>(n) + PinnedLease::part<MechParams>(n) + PinnedLease::part<GrowState>(n) +
+                      PinnedLease::part<CycleParams>(n) + PinnedLease::part<uint32_t>(n));
+    size_t off = 0;
+    PotParams* const pot = lease.take<PotParams>(off, n);
+    MechParams* const mech = lease.take<MechParams>(off, n);
+    GrowState* const grow = lease.take<GrowState>(off, n);
+    CycleParams* const cyc = lease.take<CycleParams>(off, n);
+    uint32_t* const nn = lease.take<uint32_t>(off, n);
     std::atomic<uint32_t> bad{UINT32_MAX}, rbits{0}, cbits{0};
-    parallel_for(n, [&](size_t a0, size_t a1) {
-        ParamCache k;
-        float rmax = 0.0f, cmax = 0.0f;
-        for (size_t a = a0; a < a1; ++a) {
-            s->base[a] = par[a];
-            s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, (uint64_t)a};
-            s->gslot[a] = a;
-            s->parents[a] = crm_ident{-1, 0, 0};
-            if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE) {
-                uint32_t cur = bad.load();
-                while ((uint32_t)a < cur && !bad.compare_exchange_weak(cur, (uint32_t)a)) {}
-                continue;
+    const size_t CH = (size_t)1 << 18;
+    for (size_t c0 = 0; c0 < n; c0 += CH) {
+        const size_t c1 = std::min<size_t>(n, c0 + CH);
+        parallel_for(c1 - c0, [&](size_t b0, size_t b1) {
+            const size_t a0 = c0 + b0, a1 = c0 + b1;
+            ParamCache k;
+            float rmax = 0.0f, cmax = 0.0f;
+            for (size_t a = a0; a < a1; ++a) {
+                s->base[a] = par[a];
+                s->ids[a] = crm_ident{CRM_ID_INITIAL, 0, (uint64_t)a};
+                s->gslot[a] = a;
+                s->parents[a] = crm_ident{-1, 0, 0};
+                if (par[a].potential != CRM_POT_MORSE && par[a].potential != CRM_POT_MIE) {
+                    uint32_t cur = bad.load();
+                    while ((uint32_t)a < cur && !bad.compare_exchange_weak(cur, (uint32_t)a)) {}
+                    continue;
+                }
+                fill_device_params_cached(par[a], k, pot[a], mech[a], grow[a], cyc[a]);
+                nn[a] = par[a].n_neighbors;
+                rmax = std::max(rmax, par[a].radius);
+                cmax = std::max(cmax, par[a].cutoff);
             }
-            fill_device_params_cached(par[a], k, pot[a], mech[a], grow[a], cyc[a]);
-            nn[a] = par[a].n_neighbors;
-            rmax = std::max(rmax, par[a].radius);
-            cmax = std::max(cmax, par[a].cutoff);
-        }
-        // non-negative floats order like their bit patterns
-        auto amax = [](std::atomic<uint32_t>& t, float v) {
-            if (!(v > 0.0f)) return;
-            const uint32_t b = __builtin_bit_cast(uint32_t, v);
-            uint32_t cur = t.load();
-            while (b > cur && !t.compare_exchange_weak(cur, b)) {}
-        };
-        amax(rbits, rmax);
-        amax(cbits, cmax);
-    });
+            // non-negative floats order like their bit patterns
+            auto amax = [](std::atomic<uint32_t>& t, float v) {
+                if (!(v > 0.0f)) return;
+                const uint32_t b = __builtin_bit_cast(uint32_t, v);
+                uint32_t cur = t.load();
+                while (b > cur && !t.compare_exchange_weak(cur, b)) {}
+            };
+            amax(rbits, rmax);
+            amax(cbits, cmax);
+        });
+        if (bad.load() != UINT32_MAX) break;
+        const size_t m_ = c1 - c0;
+        CK(cudaMemcpyAsync(s->d.pot + c0, pot + c0, sizeof(PotParams) * m_, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.mech + c0, mech + c0, sizeof(MechParams) * m_, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.grow + c0, grow + c0, sizeof(GrowState) * m_, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.cyc + c0, cyc + c0, sizeof(CycleParams) * m_, cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(s->d.nn + c0, nn + c0, sizeof(uint32_t) * m_, cudaMemcpyHostToDevice, s->stream));
+    }
+    tr.mark("convert+param_copies");
     if (bad.load() != UINT32_MAX) {
         CK(cudaStreamSynchronize(s->stream));
         return fail(CRM_ERR_INVALID, "rod %u: unknown potential %d", bad.load(), par[bad.load()].potential);
@@ -1193,11 +1346,6 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
     s->evals_since_build = 0;
     s->steps_since_build = 0;
     if (n) {
-        CK(cudaMemcpyAsync(s->d.pot, pot.data(), sizeof(PotParams) * n, cudaMemcpyHostToDevice, s->stream));
-        CK(cudaMemcpyAsync(s->d.mech, mech.data(), sizeof(MechParams) * n, cudaMemcpyHostToDevice, s->stream));
-        CK(cudaMemcpyAsync(s->d.grow, grow.data(), sizeof(GrowState) * n, cudaMemcpyHostToDevice, s->stream));
-        CK(cudaMemcpyAsync(s->d.cyc, cyc.data(), sizeof(CycleParams) * n, cudaMemcpyHostToDevice, s->stream));
-        CK(cudaMemcpyAsync(s->d.nn, nn.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s->stream));
         CK(cudaMemsetAsync(s->d.nhist, 0, n, s->stream));
         CK(cudaMemsetAsync(s->d.status, 0, sizeof(Status), s->stream));
         s->n = n;
@@ -1206,6 +1354,7 @@ int crm_sim_set_agents(crm_sim* s, const float* pos, const float* vel, const crm
         s->launches += 3;
         CK(cudaGetLastError());
         if ((rc = crm_read_status(s))) return rc;
+        tr.mark("bounds+wait");
         s->emax = __builtin_bit_cast(float, s->h_status->emax_bits);
         s->bounds_fresh = true;
         if (!std::isfinite(s->emax)) return fail(CRM_ERR_NUMERIC, "CalcError: non-finite initial positions");
@@ -1645,11 +1794,8 @@ void crm_host_free(void* ptr) {
 
 int crm_sim_get_state(crm_sim* s, float* pos, float* vel, crm_rod_params* par, crm_ident* ids, crm_ident* parents) {
     CK(cudaSetDevice(s->device));
-    int rc = download_state(s, pos, vel, par);
-    if (rc) return rc;
-    if (ids) memcpy(ids, s->ids.data(), sizeof(crm_ident) * s->n);
-    if (parents) memcpy(parents, s->parents.data(), sizeof(crm_ident) * s->n);
-    return 0;
+    if (s->n == 0) return 0;
+    return download_state(s, pos, vel, par, ids, parents);
 }
 
 uint32_t crm_sim_n_snapshots(const crm_sim* s) { return (uint32_t)s->snaps.size(); }

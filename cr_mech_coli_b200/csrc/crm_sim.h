@@ -112,6 +112,10 @@ struct crm_sim {
     bool lists_morse = true, lists_mie = true;  // potential types among the rods of the structure (same protocol)
     uint32_t overflow_reasons = 0;  // why builds were abandoned (bits of Status::plist_overflow), how often
     uint64_t n_overflows = 0;
+    // why steps asked for a new search (crm_sim_rebuild_reasons): 0 displacement beyond skin/2, 1 rod left the slab,
+    // 2 a rod did not fit the structure, 3 a patched row is full, 4 divisions that could not be patched,
+    // 5 no live structure (hold-off / first step / reallocation), 6 search repeated on a finer grid, 7 steps in total
+    uint64_t why_rebuild[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t lists_maxl = 32;   // longest list of the structure (sizes the staging area of the list kernel)
     bool lists_slow = true;     // ... and queues pairs with mixed potentials (known after the build step's status)
     bool want_rebuild = true;   // outcome of the last step: a local reason to rebuild (sharded runs: the
@@ -131,8 +135,10 @@ struct crm_sim {
     uint64_t n_builds = 0, n_eval_steps = 0;
     // host-side bookkeeping
     crm_hvec<crm_rod_params> base;  // cold fields per slot
-    std::vector<crm_ident> ids, parents;
-    std::vector<uint64_t> gslot;       // global slot (= slot of the unsharded run) per owned slot
+    // (default-initialised storage: every element is written before it is read, and a 1e6-rod upload must not
+    // zero-fill and page-fault 56 MB on one thread first)
+    crm_hvec<crm_ident> ids, parents;
+    crm_hvec<uint64_t> gslot;          // global slot (= slot of the unsharded run) per owned slot
     std::vector<uint64_t> vox_counter;   // [sim][user voxel]
     std::vector<uint32_t> sim_of;        // batched sims: sim index per slot (empty: one colony)
     uint32_t n_sims = 1;

@@ -232,9 +232,15 @@ int crm_sim_set_skin(crm_sim* sim, float skin);
 /* Steps that rebuilt the structure / steps that reused it. */
 int crm_sim_list_stats(const crm_sim* sim, uint64_t* n_builds, uint64_t* n_eval_steps);
 /* Builds abandoned because a rod did not fit the structure's capacities: reason bits (1: more than 32 neighbour
- * rods (16 for 9..16 vertices), 2 / 4: more than 64 queued own / ext evaluations per vertex, 8: more than 8
+ * rods (16 for 9..16 vertices), 2 / 4: more than 128 queued own / ext evaluations per vertex, 8: more than 8
  * sensing candidates per vertex), their number, and the longest list of the live structure. */
 int crm_sim_list_overflows(const crm_sim* sim, uint32_t* reasons, uint64_t* count, uint32_t* longest_list);
+/* Why steps asked for a new neighbour search (diagnostics of the persistent structure; the reference re-sorts its
+ * voxels every step, cellular_raza chili sort_cells_in_subdomains): counts of steps since the upload with
+ * [0] a vertex displaced beyond skin/2, [1] a rod that left its slab, [2] a rod that did not fit the structure,
+ * [3] a patched row that is full, [4] divisions that could not be patched, [5] no live structure (first step,
+ * hold-off, reallocation), [6] a search repeated on a finer grid, [7] steps in total. */
+int crm_sim_rebuild_reasons(const crm_sim* sim, uint64_t out[8]);
 /* Divisions while the structure is live do not force a new search: the rows of the daughters and of the
  * mothers' neighbours are rebuilt from candidate lists (the reference re-sorts its voxels every step;
  * cellular_raza chili update_cell_cycle + sort_cells_in_subdomains).  Count of division steps absorbed
