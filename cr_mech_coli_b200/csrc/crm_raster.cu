@@ -431,8 +431,11 @@ struct Outlines {
     int* status = nullptr;
 };
 
+// ev_a / ev_b (optional): recorded around the outline kernel alone (the allocations and the copies in front of it
+// stall the host, not the device, and are not kernel time)
 int outlines(Scratch& sc, Outlines& o, const float* pos, const float* radii, uint32_t n, uint32_t nv, float delta, float eps,
-             float size_x, float size_y, int res_x, int res_y, bool pixels, cudaStream_t st) {
+             float size_x, float size_y, int res_x, int res_y, bool pixels, cudaStream_t st, cudaEvent_t ev_a = nullptr,
+             cudaEvent_t ev_b = nullptr) {
     int rc;
     if ((rc = sc.alloc(o.pos, (size_t)n * nv * 3)) || (rc = sc.alloc(o.radii, n)) || (rc = sc.alloc(o.hull, (size_t)n * MAXV)) ||
         (rc = sc.alloc(o.count, n)) || (rc = sc.alloc(o.bbox, n)) || (rc = sc.alloc(o.orient, n)) || (rc = sc.alloc(o.status, 1)))
@@ -441,8 +444,10 @@ int outlines(Scratch& sc, Outlines& o, const float* pos, const float* radii, uin
     CK(cudaMemcpyAsync(o.pos, pos, sizeof(float) * (size_t)n * nv * 3, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(o.radii, radii, sizeof(float) * n, cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(o.status, 0, sizeof(int), st));
+    if (ev_a) CK(cudaEventRecord(ev_a, st));
     if (n) k_hull<<<blocks_for(n, 64), 64, 0, st>>>(o.pos, o.radii, (int)n, (int)nv, delta, eps, size_x, size_y, res_x, res_y, o.hull,
                                                     o.hull_px, o.count, o.bbox, o.bbox_px, o.orient, o.status);
+    if (ev_b) CK(cudaEventRecord(ev_b, st));
     CK(cudaGetLastError());
     int h = 0;
     CK(cudaMemcpyAsync(&h, o.status, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -496,9 +501,11 @@ int crm_render_mask_2d(const float* pos, const float* radii, const uint8_t* colo
     if (npx == 0) return 0;
     Scratch sc;
     Outlines o;
-    cudaEvent_t e0, e1;
+    cudaEvent_t e0, e1, e2, e3;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
+    CK(cudaEventCreate(&e2));
+    CK(cudaEventCreate(&e3));
     unsigned *owner, *cover;
     uint8_t *dcol, *dmask, *dover;
     int rc;
@@ -506,9 +513,10 @@ int crm_render_mask_2d(const float* pos, const float* radii, const uint8_t* colo
         (rc = sc.alloc(dmask, npx * 3)) || (rc = sc.alloc(dover, npx * 3)))
         return rc;
     CK(cudaMemcpyAsync(dcol, colors, (size_t)n * 3, cudaMemcpyHostToDevice, 0));
-    CK(cudaEventRecord(e0, 0));
-    if ((rc = outlines(sc, o, pos, radii, n, n_vertices, delta_angle, epsilon, domain_size[0], domain_size[1], rx, ry, true, 0)))
+    if ((rc = outlines(sc, o, pos, radii, n, n_vertices, delta_angle, epsilon, domain_size[0], domain_size[1], rx, ry, true, 0, e2,
+                       e3)))
         return rc;
+    CK(cudaEventRecord(e0, 0));
     CK(cudaMemsetAsync(owner, 0, sizeof(unsigned) * npx, 0));
     CK(cudaMemsetAsync(cover, 0, sizeof(unsigned) * npx, 0));
     if (n) k_raster<<<n, 128>>>(o.hull_px, o.count, o.bbox_px, rx, ry, owner, cover);
@@ -518,13 +526,16 @@ int crm_render_mask_2d(const float* pos, const float* radii, const uint8_t* colo
     CK(cudaMemcpyAsync(out_mask, dmask, npx * 3, cudaMemcpyDeviceToHost, 0));
     CK(cudaMemcpyAsync(out_overlap, dover, npx * 3, cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
-    if (kernel_ms) {
-        float ms = 0.0f;
+    if (kernel_ms) {  // outline kernel + (clear, raster, resolve): the host's wait for the outline status is not in it
+        float ms = 0.0f, ms_hull = 0.0f;
         CK(cudaEventElapsedTime(&ms, e0, e1));
-        *kernel_ms = ms;
+        CK(cudaEventElapsedTime(&ms_hull, e2, e3));
+        *kernel_ms = (double)ms + (double)ms_hull;
     }
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    cudaEventDestroy(e2);
+    cudaEventDestroy(e3);
     return 0;
 }
 

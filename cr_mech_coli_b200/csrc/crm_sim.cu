@@ -652,11 +652,13 @@ static int launch_neighbour_and_force(crm_sim* s, bool count, bool build = false
     return 0;
 }
 
-// list entries the list kernel stages per rod: the longest list of the live structure, rounded up to 4 (rows that a
-// division is about to patch grow by at most PATCH_EXTRA candidates before the host hears of their new length)
+// list entries the list kernel stages per rod: exactly the longest list of the live structure (rows that a division
+// is about to patch grow by at most PATCH_EXTRA candidates before the host hears of their new length).  Not rounded
+// up: at 8 vertices 8 entries leave room for 8 resident blocks per SM, 9 for 7, 12 for 6 (a slab of a sharded
+// lattice lists 9 where the whole colony lists 8: rounding to 12 cost 13 % of the list step).
 static void set_staging(crm_sim* s, bool rows_pending) {
     const int cap = s->lp > 8 ? 16 : 32;
-    const int m = std::max(4, (int)(s->lists_maxl + (rows_pending ? (uint32_t)PATCH_EXTRA : 0u) + 3u) / 4 * 4);
+    const int m = std::max(1, (int)(s->lists_maxl + (rows_pending ? (uint32_t)PATCH_EXTRA : 0u)));
     s->d.maxl = std::min(m, cap);
 }
 
