@@ -660,6 +660,9 @@ static void set_staging(crm_sim* s, bool rows_pending) {
     const int cap = s->lp > 8 ? 16 : 32;
     const int m = std::max(1, (int)(s->lists_maxl + (rows_pending ? (uint32_t)PATCH_EXTRA : 0u)));
     s->d.maxl = std::min(m, cap);
+    // (Staging the records in passes of 8 rods, so that the footprint does not follow the longest list, was built and
+    // measured: the per-entry pass check and the cursors held across passes cost 10 % of a single-pass step, and
+    // the relaxed lattice with one list of 13 rods ran no faster: 0.99 vs 0.93 ms.  Not kept.)
 }
 
 // the list step can run force + mechanics in ONE kernel (k_force_eval<.., FUSE>): fast math, no mixed pairs
@@ -1197,6 +1200,43 @@ int crm_sim_list_overflows(const crm_sim* s, uint32_t* reasons, uint64_t* count,
     if (reasons) *reasons = s->overflow_reasons;
     if (count) *count = s->n_overflows;
     if (longest_list) *longest_list = s->lists_maxl;
+    return 0;
+}
+
+// totals over the rows of the live structure (diagnostics): queued own / ext evaluations, sensing candidates,
+// listed rods; rows of owned rods only
+__global__ void k_list_totals(const uint32_t* __restrict__ pnq, const uint32_t* __restrict__ sorted, uint32_t n, uint32_t n_own,
+                              int lp, unsigned long long* __restrict__ out) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long o = 0, e = 0, q = 0, c = 0;
+    if (g < n && sorted[g] < n_own) {
+        for (int l = 0; l < lp; ++l) {
+            const uint32_t w = pnq[(size_t)g * lp + l];
+            if ((w >> 24) == 0xffu) continue;
+            o += w & 0xffu; e += (w >> 8) & 0xffu; q += (w >> 16) & 0xffu;
+            if (l == 0) c += w >> 24;
+        }
+    }
+    for (int k = 16; k > 0; k >>= 1) {
+        o += __shfl_xor_sync(0xffffffffu, o, k); e += __shfl_xor_sync(0xffffffffu, e, k);
+        q += __shfl_xor_sync(0xffffffffu, q, k); c += __shfl_xor_sync(0xffffffffu, c, k);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(out, o); atomicAdd(out + 1, e); atomicAdd(out + 2, q); atomicAdd(out + 3, c); }
+}
+
+int crm_sim_list_totals(crm_sim* s, uint64_t out[4]) {
+    if (!s || !out) return fail(CRM_ERR_INVALID, "null argument");
+    out[0] = out[1] = out[2] = out[3] = 0;
+    if (!s->have_lists || s->n == 0) return 0;
+    CK(cudaSetDevice(s->device));
+    unsigned long long* d_out = reinterpret_cast<unsigned long long*>(s->stage);  // (scratch: nothing else is in flight)
+    CK(cudaStreamSynchronize(s->stream));
+    CK(cudaMemsetAsync(d_out, 0, 4 * sizeof(unsigned long long), s->stream));
+    const uint32_t n = s->n + s->n_ghost;
+    k_list_totals<<<blocks_for(n, 256), 256, 0, s->stream>>>(s->d.pnq, s->d.sorted, n, s->n, s->lp, d_out);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, d_out, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
     return 0;
 }
 
