@@ -166,7 +166,7 @@ class Library:
             "sim_set_solver_order": (C.c_int, [vp, C.c_int]),
             "sim_set_spring_end_weight": (C.c_int, [vp, C.c_float]),
             "sim_rebuild_reasons": (C.c_int, [vp, C.c_uint64 * 8]),
-            "sim_list_totals": (C.c_int, [vp, C.c_uint64 * 4]),
+            "sim_list_totals": (C.c_int, [vp, C.c_uint64 * 6]),
             "sim_list_stats": (C.c_int, [vp, P(u64), P(u64)]),
             "sim_list_overflows": (C.c_int, [vp, P(u32), P(u64), P(u32)]),
             "microbench": (C.c_int, [C.c_int, P(C.c_double), P(C.c_double), P(C.c_double)]),
@@ -402,9 +402,10 @@ class Sim:
 
     def list_totals(self):
         """Queued evaluations and listed rods of the live neighbour structure (zeros if there is none)."""
-        w = (C.c_uint64 * 4)()
+        w = (C.c_uint64 * 6)()
         self.L.check(self.L.fn("sim_list_totals")(self.h, w))
-        return dict(zip(("own_evaluations", "ext_evaluations", "sensing_candidates", "listed_rods"), map(int, w)))
+        return dict(zip(("own_evaluations", "ext_evaluations", "sensing_candidates", "listed_rods", "long_rows",
+                         "two_launch_steps"), map(int, w)))
 
     def last_forces(self):
         f = np.zeros((self.n_rods, self.n_vertices, 3), dtype=np.float32)

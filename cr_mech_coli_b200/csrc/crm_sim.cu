@@ -179,6 +179,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     G(s->d.dsib, 0, (size_t)cap);
     items.back().fill = 0xff;
     G(s->d.dirty_list, 0, (size_t)cap);
+    G(s->long_rows, 0, (size_t)cap);
     G(s->d.dirty_n, 0, (size_t)1);
     G(s->d.cell_of, 0, (size_t)cap);
     G(s->d.cell_rank, 0, (size_t)cap);
@@ -215,6 +216,7 @@ int crm_reserve(crm_sim* s, uint32_t need) {
     }
     s->arena = arena;
     s->n_dirty = 0;
+    s->n_long = 0;
     s->need_rebuild = true;  // the structure does not survive a reallocation
     s->have_lists = false;
     s->d.divcap = cap;
@@ -665,6 +667,59 @@ static void set_staging(crm_sim* s, bool rows_pending) {
     // the relaxed lattice with one list of 13 rods ran no faster: 0.99 vs 0.93 ms.  Not kept.)
 }
 
+// Rows in two classes.  The staging area of the list kernel is sized for the longest list it serves, and one rod that
+// lists 13 others leaves 6 resident blocks per SM where 8 entries leave 8.  So lists of up to short_maxl rods
+// (the longest staging that still leaves 7 blocks) are served by the main launch over all rows, which skips
+// longer rows, and those (k_classify_rows collects them after every (re)build of rows) by a second launch
+// over just them.  Results do not depend on the split: a row's arithmetic is the same in either launch.
+static int short_maxl(const crm_sim* s) {
+    const int cap = s->lp > 8 ? 16 : 32;
+    int t = 4;
+    while (t < cap && (232448 / (list_kernel_smem(s->lp, t + 1, true) + 1024)) >= 7) ++t;
+    return t;
+}
+
+__global__ void k_classify_rows(const uint32_t* __restrict__ pnq, uint32_t n, int lp, uint32_t thr, uint32_t* __restrict__ rows,
+                                Status* st) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const uint32_t c = pnq[(size_t)g * lp] >> 24;
+    if (c != 0xffu && c > thr) rows[atomicAdd(&st->n_long, 1u)] = g;
+}
+
+// after a (re)build of rows, in the same step: the long rows of the structure as it is now
+static int classify_rows(crm_sim* s) {
+    const uint32_t n = s->n + s->n_ghost;
+    if (n == 0) return 0;
+    k_classify_rows<<<blocks_for(n, 256), 256, 0, s->stream>>>(s->d.pnq, n, s->lp, (uint32_t)short_maxl(s), s->long_rows, s->d.status);
+    s->launches += 1;
+    s->classified = true;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// the list kernel(s) of one step; s->d.maxl = longest list (set_staging).  `all_rows`: rows were rebuilt in front of
+// this launch, the classes are stale: one launch staged for the longest list.
+static int launch_list_step(crm_sim* s, bool uniform, int pt, bool fuse, bool all_rows) {
+    s->d.rows = nullptr;
+    s->d.n_rows = 0;
+    if (all_rows || s->n_long == 0 || s->d.maxl <= short_maxl(s)) {
+        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, fuse, s->stream);
+        s->launches += 1;
+        return 0;
+    }
+    Dev da = s->d;
+    da.maxl = short_maxl(s);
+    launch_force_eval(s->nv, da, s->fast_math, uniform, pt, fuse, s->stream);
+    Dev db = s->d;
+    db.rows = s->long_rows;
+    db.n_rows = s->n_long;
+    launch_force_eval(s->nv, db, s->fast_math, uniform, pt, fuse, s->stream);
+    s->launches += 2;
+    s->n_two_class_steps += 1;
+    return 0;
+}
+
 // the list step can run force + mechanics in ONE kernel (k_force_eval<.., FUSE>): fast math, no mixed pairs
 static bool fusable(const crm_sim* s) { return s->fused && s->fast_math && !s->lists_slow; }
 // after a fused step the buffer it wrote holds the current vertex records
@@ -695,12 +750,11 @@ static int launch_force_from_lists(crm_sim* s) {
     // force + mechanics in one kernel, also when rows were rebuilt in front of it (a row that did not fit keeps
     // the force the rebuild computed: the fused kernel integrates such a rod with that force)
     s->step_fused = fusable(s);
-    (void)rows_rebuilt;
     if (s->step_fused) s->d.vrec_out = s->vrec_alt;
-    launch_force_eval(s->nv, s->d, s->fast_math, !s->lists_slow, pt, s->step_fused, s->stream);
+    int rc = launch_list_step(s, !s->lists_slow, pt, s->step_fused, rows_rebuilt);
     if (s->timers) CK(cudaEventRecord(s->ev1, s->stream));
-    s->launches += 1;
-    return 0;
+    if (rc) return rc;
+    return rows_rebuilt ? classify_rows(s) : 0;
 }
 
 // [n_div, reason to rebuild, error code, 0] of the step just enqueued, for the sharded coordinator's all_gather
@@ -758,6 +812,7 @@ static int step_enqueue_open(crm_sim* s, uint32_t* dev_flags) {
                 s->backoff = std::min<uint32_t>(s->backoff * 2, 512);
                 s->short_builds = 0;
             }
+            if (!rc) rc = classify_rows(s);
             s->n_builds += 1;
             s->steps_since_build = 0;
             s->evals_since_build = 0;
@@ -796,6 +851,10 @@ static int step_conclude(crm_sim* s) {
     if ((rc = crm_report_device_error(s))) return rc;
     const uint32_t n_div = s->h_status->n_div;
     bool want = s->h_status->n_leave > 0;
+    if (s->classified) {  // rows were (re)built in this step: the long rows of the structure as it is now
+        s->n_long = s->h_status->n_long;
+        s->classified = false;
+    }
     s->why_rebuild[7] += 1;
     if (want) s->why_rebuild[1] += 1;
     if (persistent(s)) {
@@ -910,7 +969,7 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
         s->d.iteration = it0 + k + 1;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
         if (fuse) s->d.vrec_out = s->vrec_alt;
-        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, fuse, s->stream);
+        launch_list_step(s, uniform, pt, fuse, false);
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev1, s->stream));
         if (fuse) {
             swap_vrec(s);
@@ -921,7 +980,7 @@ static int step_batch(crm_sim* s, uint32_t n_max, uint32_t* done) {
         }
     }
     s->d.latch = nullptr;
-    s->launches += (fuse ? 1ull : 2ull) * B;
+    s->launches += (fuse ? 0ull : 1ull) * B;
     s->bounds_fresh = false;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(s->h_status, s->d.status, sizeof(Status), cudaMemcpyDeviceToHost, s->stream));
@@ -1224,9 +1283,11 @@ __global__ void k_list_totals(const uint32_t* __restrict__ pnq, const uint32_t* 
     if ((threadIdx.x & 31) == 0) { atomicAdd(out, o); atomicAdd(out + 1, e); atomicAdd(out + 2, q); atomicAdd(out + 3, c); }
 }
 
-int crm_sim_list_totals(crm_sim* s, uint64_t out[4]) {
+int crm_sim_list_totals(crm_sim* s, uint64_t out[6]) {
     if (!s || !out) return fail(CRM_ERR_INVALID, "null argument");
     out[0] = out[1] = out[2] = out[3] = 0;
+    out[4] = s->have_lists ? s->n_long : 0;
+    out[5] = s->n_two_class_steps;
     if (!s->have_lists || s->n == 0) return 0;
     CK(cudaSetDevice(s->device));
     unsigned long long* d_out = reinterpret_cast<unsigned long long*>(s->stage);  // (scratch: nothing else is in flight)
@@ -1662,7 +1723,7 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
         if ((rc = crm_shard_unpack_all(s, rlo, rhi, all_flags, world, s->latch_buf, (uint32_t)(it0 + k)))) break;
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev0, s->stream));
         if (fuse) s->d.vrec_out = s->vrec_alt;
-        launch_force_eval(s->nv, s->d, s->fast_math, uniform, pt, fuse, s->stream);
+        launch_list_step(s, uniform, pt, fuse, false);
         if (s->timers && k == 0) CK(cudaEventRecord(s->ev1, s->stream));
         if (fuse) {
             swap_vrec(s);
@@ -1672,7 +1733,7 @@ int crm_sim_steps_sharded(crm_sim* s, uint32_t n_max, void* send_lo, void* send_
             launch_integrate(s->nv, s->d, s->stream);
             if (s->timers && k == 0) CK(cudaEventRecord(s->ev3, s->stream));
         }
-        s->launches += fuse ? 1 : 2;
+        s->launches += fuse ? 0 : 1;
     }
     if (!rc) {  // the flags of the last step (the host's copy; the latch of a full batch stays 0 unless it fired)
         k_status_flags<<<1, 1, 0, s->stream>>>(s->d.status, s->skin, 0u, my_flags);

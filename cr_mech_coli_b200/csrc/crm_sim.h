@@ -37,6 +37,7 @@ void launch_bounds_kernel(int nv, const Dev& d, cudaStream_t st);
 int launch_binning(const Dev& d, uint32_t n_tiles, cudaStream_t st);
 void launch_force(int nv, const Dev& d, bool fast, bool count, bool build, cudaStream_t st);
 bool launch_force_eval(int nv, const Dev& d, bool fast, bool uniform, int pot_type, bool fused, cudaStream_t st);
+size_t list_kernel_smem(int lp, int maxl, bool fused);
 void launch_force_lists(int nv, const Dev& d, bool fast, cudaStream_t st);
 int launch_patch(const Dev& d, uint32_t n_div, uint32_t n0, int lp, int maxp, cudaStream_t st);
 void launch_integrate(int nv, const Dev& d, cudaStream_t st);
@@ -128,6 +129,12 @@ struct crm_sim {
     uint32_t short_builds = 0;  // consecutive rebuilds whose lists served fewer than 2 steps
     uint32_t evals_since_build = 0;
     uint32_t n_dirty = 0;       // rows queued for k_force<LISTS> before the next list step (divisions)
+    // rows in two classes: lists of up to `short_maxl` rods are staged by the main launch of a list step (sized for
+    // 7+ resident blocks per SM), the n_long longer ones (long_rows, from k_classify_rows) by a second, small launch
+    uint32_t* long_rows = nullptr;
+    uint32_t n_long = 0;
+    bool classified = false;    // this step's status block carries a fresh Status::n_long
+    uint64_t n_two_class_steps = 0;
     uint32_t n_patches = 0;     // division steps absorbed without a new search
     bool patching = true;       // CRM_B200_PATCH=0 / crm_sim_set_patching: search again after every division
     bool patch_divisions = false;  // set by the step that saw divisions and no other reason to search again

@@ -242,9 +242,11 @@ int crm_sim_list_overflows(const crm_sim* sim, uint32_t* reasons, uint64_t* coun
  * hold-off, reallocation), [6] a search repeated on a finer grid, [7] steps in total. */
 int crm_sim_rebuild_reasons(const crm_sim* sim, uint64_t out[8]);
 /* Totals over the live structure (diagnostics; no counterpart in the reference, whose voxel stencil holds no such
- * state): [0] queued own evaluations, [1] queued ext evaluations, [2] sensing candidates, [3] listed rods.  What a
- * list step evaluates per launch is out[0] + out[1]; zeros when no structure is live. */
-int crm_sim_list_totals(crm_sim* sim, uint64_t out[4]);
+ * state): [0] queued own evaluations, [1] queued ext evaluations, [2] sensing candidates, [3] listed rods, [4] rows
+ * whose list is too long for the main launch of a list step (served by a second, small launch), [5] list steps so far
+ * that ran as those two launches.  What a list step evaluates is out[0] + out[1]; [0..4] are zero when no structure
+ * is live. */
+int crm_sim_list_totals(crm_sim* sim, uint64_t out[6]);
 /* Divisions while the structure is live do not force a new search: the rows of the daughters and of the
  * mothers' neighbours are rebuilt from candidate lists (the reference re-sorts its voxels every step;
  * cellular_raza chili update_cell_cycle + sort_cells_in_subdomains).  Count of division steps absorbed

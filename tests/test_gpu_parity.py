@@ -648,6 +648,10 @@ def test_lists_with_more_than_16_partners(product_lib):
     st = g.list_stats()
     assert st["longest_list"] > 16 and st["overflows"] == 0, st
     assert st["eval_steps"] >= 40, st
+    # rows in two classes: the rods at the rim list few others and are served by the main launch, the stacked
+    # interior (lists beyond its staging) by the launch over the long rows
+    tot = g.list_totals()
+    assert 0 < tot["long_rows"] < len(pos) and tot["two_launch_steps"] >= 40, tot
     for (it, pg, vg, parg, *_), (_, po, vo, paro, *_) in zip(g.snapshots(), o.snapshots()):
         assert np.abs(pg - po).max() < TRAJ_ATOL, f"iteration {it}: {np.abs(pg - po).max()}"
         assert (parg["n_neighbors"] == paro["n_neighbors"]).all()
