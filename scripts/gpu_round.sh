@@ -14,7 +14,5 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
    python bench.py --steps 20 --warmup 5 --no-cpu --no-long-run --e2e-reps 1 > gpurun_out/ncu_launch.log 2>&1; echo "ncu_list rc=$?" | tee -a gpurun_out/rc.txt
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'^k_force_eval$' -s 6 -c 1 -f -o gpurun_out/fused_eval \
    python bench.py --steps 20 --warmup 5 --no-cpu --no-long-run --e2e-reps 1 > gpurun_out/ncu_full.log 2>&1; echo "ncu_full rc=$?" | tee -a gpurun_out/rc.txt
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:'^k_force$' -s 4 -c 1 -f -o gpurun_out/search_c4 \
-   python bench.py --config c4 --steps 10 --warmup 3 --no-cpu --no-long-run --e2e-reps 1 > gpurun_out/ncu_search.log 2>&1; echo "ncu_search rc=$?" | tee -a gpurun_out/rc.txt
 tail -12 gpurun_out/pytest_gpu.log; tail -3 gpurun_out/pytest_noalloc_alone.log; python scripts/bench_short.py < gpurun_out/bench_c3_n1.json; grep "crm trace" gpurun_out/bench_c3_n1.err | tail -2
 for c in c2 c4 c5; do python scripts/bench_short.py < gpurun_out/bench_${c}_n1.json | head -1; done; cat gpurun_out/raster.jsonl | cut -c1-400; tail -3 gpurun_out/raster.err
