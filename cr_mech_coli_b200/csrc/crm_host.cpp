@@ -4,6 +4,8 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <mutex>
+#include <new>
 #include <string>
 #include <utility>
 #include <vector>
@@ -192,3 +194,73 @@ int crm_generate_positions(uint32_t n_agents, float spring_length, const crm_con
 }
 
 }  // extern "C"
+
+// ---- recycled host blocks (crm_hvec's allocator) ------------------------------------------------------------------
+// Blocks of 1 MB and more are kept when freed (at most HOST_CACHE_LIMIT bytes, best fit within 2x on reuse): their
+// pages are resident, so the next simulation's mirrors do not fault them in again.  Smaller blocks go straight to
+// operator new / delete.
+namespace {
+constexpr size_t HOST_CACHE_MIN = (size_t)1 << 20, HOST_CACHE_LIMIT = (size_t)1 << 30;
+struct HostBlockCache {
+    std::mutex m;
+    std::vector<std::pair<void*, size_t>> free_blocks;   // (block, capacity)
+    std::vector<std::pair<void*, size_t>> live_big;      // capacity of the big blocks handed out
+    size_t held = 0;
+    ~HostBlockCache() {
+        for (auto& b : free_blocks) ::operator delete(b.first);
+    }
+};
+HostBlockCache& host_cache() {
+    static HostBlockCache* c = new HostBlockCache();  // (never destroyed: vectors of static objects may outlive it)
+    return *c;
+}
+}  // namespace
+
+void* crm_host_block_alloc(size_t bytes) {
+    if (bytes < HOST_CACHE_MIN) return ::operator new(bytes ? bytes : 1);
+    HostBlockCache& c = host_cache();
+    {
+        std::lock_guard<std::mutex> lock(c.m);
+        size_t best = SIZE_MAX, best_i = 0;
+        for (size_t i = 0; i < c.free_blocks.size(); ++i) {
+            const size_t cap = c.free_blocks[i].second;
+            if (cap >= bytes && cap <= 2 * bytes && cap < best) { best = cap; best_i = i; }
+        }
+        if (best != SIZE_MAX) {
+            void* p = c.free_blocks[best_i].first;
+            c.free_blocks.erase(c.free_blocks.begin() + (long)best_i);
+            c.held -= best;
+            c.live_big.emplace_back(p, best);
+            return p;
+        }
+    }
+    void* p = ::operator new(bytes);
+    std::lock_guard<std::mutex> lock(c.m);
+    c.live_big.emplace_back(p, bytes);
+    return p;
+}
+
+void crm_host_block_free(void* p, size_t bytes) noexcept {
+    if (!p) return;
+    if (bytes < HOST_CACHE_MIN) {
+        ::operator delete(p);
+        return;
+    }
+    HostBlockCache& c = host_cache();
+    size_t cap = 0;
+    {
+        std::lock_guard<std::mutex> lock(c.m);
+        for (size_t i = 0; i < c.live_big.size(); ++i)
+            if (c.live_big[i].first == p) {
+                cap = c.live_big[i].second;
+                c.live_big.erase(c.live_big.begin() + (long)i);
+                break;
+            }
+        if (cap && c.held + cap <= HOST_CACHE_LIMIT) {
+            c.free_blocks.emplace_back(p, cap);
+            c.held += cap;
+            return;
+        }
+    }
+    ::operator delete(p);
+}

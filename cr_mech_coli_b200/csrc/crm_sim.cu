@@ -679,10 +679,10 @@ static int short_maxl(const crm_sim* s) {
     return t;
 }
 
-__global__ void k_classify_rows(const uint32_t* __restrict__ pnq, uint32_t n, int lp, uint32_t thr, uint32_t* __restrict__ rows,
-                                Status* st) {
+__global__ void k_classify_rows(const uint32_t* __restrict__ pnq, const uint32_t* __restrict__ sorted, uint32_t n, uint32_t n_own,
+                                int lp, uint32_t thr, uint32_t* __restrict__ rows, Status* st) {
     const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= n) return;
+    if (g >= n || sorted[g] >= n_own) return;  // (rows of ghost rods are never written: whatever they hold is stale)
     const uint32_t c = pnq[(size_t)g * lp] >> 24;
     if (c != 0xffu && c > thr) rows[atomicAdd(&st->n_long, 1u)] = g;
 }
@@ -691,7 +691,8 @@ __global__ void k_classify_rows(const uint32_t* __restrict__ pnq, uint32_t n, in
 static int classify_rows(crm_sim* s) {
     const uint32_t n = s->n + s->n_ghost;
     if (n == 0) return 0;
-    k_classify_rows<<<blocks_for(n, 256), 256, 0, s->stream>>>(s->d.pnq, n, s->lp, (uint32_t)short_maxl(s), s->long_rows, s->d.status);
+    k_classify_rows<<<blocks_for(n, 256), 256, 0, s->stream>>>(s->d.pnq, s->d.sorted, n, s->n, s->lp, (uint32_t)short_maxl(s),
+                                                               s->long_rows, s->d.status);
     s->launches += 1;
     s->classified = true;
     CK(cudaGetLastError());

@@ -18,10 +18,17 @@
 
 // std::vector whose resize() leaves trivially constructible elements uninitialised: the 1e6-rod host
 // mirrors are written right after they are sized, a zero fill first would only cost bus time.
+// Large blocks come from (and go back to) a process-wide cache (crm_host.cpp): a simulation of 1e6 rods sizes ~260 MB of
+// host mirrors, and fresh pages cost a fault each when they are first written (~40 core-ms per upload, all of it in
+// the timed region of every repeated run_simulation call and multiplied by the ranks sharing a host).
+void* crm_host_block_alloc(size_t bytes);
+void crm_host_block_free(void* p, size_t bytes) noexcept;
 template <class T>
 struct crm_default_init_alloc : std::allocator<T> {
     template <class U> struct rebind { using other = crm_default_init_alloc<U>; };
     using std::allocator<T>::allocator;
+    T* allocate(size_t n) { return static_cast<T*>(crm_host_block_alloc(n * sizeof(T))); }
+    void deallocate(T* p, size_t n) noexcept { crm_host_block_free(p, n * sizeof(T)); }
     template <class U> void construct(U* p) noexcept(std::is_nothrow_default_constructible<U>::value) { ::new (static_cast<void*>(p)) U; }
     template <class U, class... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
 };
