@@ -50,8 +50,16 @@ int crm_fail(int code, const char* fmt, ...) {
 // Work split over host threads (upload / download of 1e6-rod parameter blocks is host-bound otherwise).
 template <class F>
 static void parallel_for(size_t n, F f) {
-    const unsigned hw = std::thread::hardware_concurrency();
-    const size_t nt = std::min<size_t>(std::min<unsigned>(hw ? hw : 1u, 16u), n / 16384);
+    // (several ranks of one job share the host's cores: LOCAL_WORLD_SIZE, set by torchrun, divides them up;
+    // CRM_B200_HOST_THREADS overrides)
+    static const unsigned share = [] {
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        if (const char* e = getenv("CRM_B200_HOST_THREADS")) return (unsigned)std::max(1, atoi(e));
+        unsigned ranks = 1;
+        if (const char* e = getenv("LOCAL_WORLD_SIZE")) ranks = (unsigned)std::max(1, atoi(e));
+        return std::max(1u, std::min(16u, hw / ranks));
+    }();
+    const size_t nt = std::min<size_t>(share, n / 16384);
     if (nt <= 1) {
         f((size_t)0, n);
         return;
