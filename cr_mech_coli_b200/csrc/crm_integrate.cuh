@@ -104,13 +104,10 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
     const float L = gs.z;
     if (skip_step) return;
 
-    // neighbours
-    float Pn[3], Pp[3];
+    // next vertex (the connection to the previous one is the previous lane's connection to this one, below)
+    float Pn[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        Pn[c] = __shfl_down_sync(gm, P[c], 1, LP);
-        Pp[c] = __shfl_up_sync(gm, P[c], 1, LP);
-    }
+    for (int c = 0; c < 3; ++c) Pn[c] = __shfl_down_sync(gm, P[c], 1, LP);
     // spring of segment l (between l and l+1): force on vertex l
     float fs[3] = {0.f, 0.f, 0.f};
     float c2[3] = {P[0] - Pn[0], P[1] - Pn[1], P[2] - Pn[2]};  // conn_l = v_l - v_{l+1}
@@ -126,8 +123,15 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
     // bending at interior vertex l
     float fb[3] = {0.f, 0.f, 0.f};
     {
-        float c1[3] = {Pp[0] - P[0], Pp[1] - P[1], Pp[2] - P[2]};  // conn_{l-1}
-        float n1 = sqrtf(c1[0] * c1[0] + c1[1] * c1[1] + c1[2] * c1[2]);
+        // conn_{l-1} = v_{l-1} - v_l, its length and its unit vector are what lane l-1 has just computed as its
+        // (c2, n2, u2): the same operations on the same operands, taken over instead of being repeated
+        float c1[3], u1[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            c1[c] = __shfl_up_sync(gm, c2[c], 1, LP);
+            u1[c] = __shfl_up_sync(gm, u2[c], 1, LP);
+        }
+        const float n1 = __shfl_up_sync(gm, n2, 1, LP);
         if (l >= 1 && l < NV - 1) {
             float angle;
             if (n1 == 0.0f || n2 == 0.0f) {
@@ -138,8 +142,7 @@ __device__ __forceinline__ void integrate_rod(const Dev& d, const uint32_t a, co
                 cs = fminf(fmaxf(cs, -1.0f), 1.0f);
                 angle = acosf(cs);
             }
-            const float y1 = rcp_refined(n1);
-            float fd[3] = {div_rn(c1[0], n1, y1) - u2[0], div_rn(c1[1], n1, y1) - u2[1], div_rn(c1[2], n1, y1) - u2[2]};
+            float fd[3] = {u1[0] - u2[0], u1[1] - u2[1], u1[2] - u2[2]};
             float nfd = sqrtf(fd[0] * fd[0] + fd[1] * fd[1] + fd[2] * fd[2]);
             float scale = rigidity * (3.14159265358979323846f - angle);
             const float yf = rcp_refined(nfd);
